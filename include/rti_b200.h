@@ -1,0 +1,180 @@
+/*
+ * rti_b200.h -- C ABI of the B200-native (sm_100a) per-pixel reflectance
+ * fitting path of bara96/Smartphone-based-RTI.
+ *
+ * The reference has no FFI: the path is a set of Python functions in
+ * analysis.py that analysis.compute() calls in sequence.  Each entry point
+ * below states the reference function / lines whose arithmetic it replaces;
+ * the Python host layer (smartphone-based-rti_b200/analysis.py) binds these
+ * with ctypes and re-exposes the reference's own call surface.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross this boundary;
+ *   - "d_" pointers are device pointers on the CURRENT CUDA device, "h_"
+ *     pointers are host pointers (pinned memory makes the copies asynchronous);
+ *   - the caller owns every buffer; the library never frees caller memory;
+ *   - device entry points are asynchronous on `stream` (a cudaStream_t passed
+ *     as void*; NULL = default stream) and re-entrant across streams/devices;
+ *   - return value: 0 = ok, < 0 = bad argument, > 0 = CUDA / numerical error;
+ *     rti_last_error_string() describes the last failure on this thread;
+ *   - pixel index p = y * cols + x over a row slab [row0, row0 + rows) of the
+ *     ROI; y is the GLOBAL ROI row (row0 + local row) because the pixel
+ *     position enters the light vector (analysis.py:228-229);
+ *   - coefficient maps are planar: coef[k * plane_stride + p], k = 0..5, in the
+ *     reference's term order (lu^2, lv^2, lu*lv, lu, lv, 1) (analysis.py:285).
+ */
+#ifndef RTI_B200_H_
+#define RTI_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTI_OK 0
+#define RTI_ERR_ARG (-1)        /* NULL / negative / inconsistent argument                */
+#define RTI_ERR_TOO_FEW (-2)    /* PTM with N < 6 (reference: ValueError, analysis.py:296) */
+#define RTI_ERR_CUDA 1          /* CUDA runtime error                                      */
+#define RTI_ERR_SINGULAR 2      /* >= 1 pixel has a singular system (reference: garbage /
+                                   scipy LinAlgError for duplicate RBF nodes)              */
+#define RTI_ERR_NONFINITE 3     /* a table value is NaN/inf/out of int32 (reference:
+                                   ValueError / OverflowError at analysis.py:407)          */
+
+typedef void *rti_stream_t;     /* cudaStream_t */
+
+/* ---- library ----------------------------------------------------------------- */
+int rti_version(void);                       /* 10000*major + 100*minor + patch */
+const char *rti_last_error_string(void);
+/* SM count / total bytes of HBM of CUDA device `device`. */
+int rti_device_info(int device, int *sm_count, int64_t *hbm_bytes);
+/* Number of kernels this library has launched on this thread's behalf since the
+ * last call with reset != 0 (bench.py's gpu_launches). */
+int64_t rti_launch_count(int reset);
+
+/* ---- (1) gather: compute_intensities, analysis.py:196-246 ----------------------
+ * d_frames: uint8, points at pixel (x=0, y=row0) of frame 0; the slab of frame i
+ * starts at d_frames + i*frame_stride and is row-major [yl][x] (the ROI layout of
+ * FeatureMatcher.py:183-184), i.e. slab pixel p = yl*cols + x is byte p.  For a
+ * whole-ROI stack [n][R][R], frame_stride = R*R and d_frames = base + row0*cols.
+ * d_cams: float64 [n][3] camera positions.
+ * Outputs, each [rows*cols][n] with the light index fastest (analysis.py:217-219):
+ * d_lx/d_ly float32 = l[0], l[1] of l = (cam - p)/||cam - p|| evaluated in fp64
+ * and rounded to float32; d_inten int32. */
+int rti_gather_soa(const uint8_t *d_frames, int64_t frame_stride, const double *d_cams,
+                   int n, int row0, int rows, int cols,
+                   float *d_lx, float *d_ly, int32_t *d_inten, rti_stream_t stream);
+
+/* ---- (2) PTM fit: _interpolate_PTM analysis.py:282-298 -------------------------
+ * Least-squares fit of the 6 biquadratic coefficients per pixel.  The reference
+ * solves by full SVD; these kernels accumulate the 6x6 normal equations of the
+ * same design matrix in fp64 and solve them by an in-register Cholesky, which
+ * is the same solution for full-rank pixels.  d_bad (int32, may be NULL) is
+ * incremented once per pixel whose system is not positive definite; those
+ * pixels' coefficients are NaN.  d_coef: float64 [6][plane_stride]. */
+
+/* fused: straight from the uint8 frames, no SoA materialisation */
+int rti_ptm_fit_frames(const uint8_t *d_frames, int64_t frame_stride, const double *d_cams,
+                       int n, int row0, int rows, int cols,
+                       double *d_coef, int64_t plane_stride, int32_t *d_bad,
+                       rti_stream_t stream);
+/* from materialised (lx, ly, intensity) arrays as rti_gather_soa /
+ * compute_intensities produce them: one warp per pixel, shuffle reduction */
+int rti_ptm_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten,
+                    int64_t n_pixels, int n,
+                    double *d_coef, int64_t plane_stride, int32_t *d_bad, rti_stream_t stream);
+/* shared-light fast path: every pixel sees the same (lx_i, ly_i), so the fit is
+ * coef[6][P] = pinv[6][n] . I[n][P] with the 6 x n pseudo-inverse of the common
+ * design matrix precomputed by the caller (fp64). */
+int rti_ptm_fit_shared(const uint8_t *d_frames, int64_t frame_stride, const double *d_pinv,
+                       int n, int64_t n_pixels,
+                       double *d_coef, int64_t plane_stride, rti_stream_t stream);
+
+/* ---- (4) light-grid evaluation ----------------------------------------------------
+ * d_axis: float64 [g] grid axis values (analysis.py:345-347; the same axis is
+ * used for lu and lv).  Value at (v, u): a0*lu^2 + a1*lv^2 + a2*lu*lv + a3*lu +
+ * a4*lv + a5 with lu = axis[u], lv = axis[v] (analysis.py:303-313), fp64. */
+
+/* prepare_images_data layout (analysis.py:400-409): d_table int32
+ * [g][g][image_stride], image (v, u) holds pixel p at p; the fp64 value is
+ * truncated toward zero like the reference's element assignment.  d_bad counts
+ * pixels whose values cannot be represented (NaN/inf/|.| >= 2^31). */
+int rti_ptm_table(const double *d_coef, int64_t plane_stride, int64_t n_pixels,
+                  const double *d_axis, int g,
+                  int32_t *d_table, int64_t image_stride, int32_t *d_bad, rti_stream_t stream);
+/* interpolate_intensities layout (analysis.py:349, 372): d_grids float64
+ * [n_pixels][g][g], pixel-major, indexed [ly][lx]. */
+int rti_ptm_grids(const double *d_coef, int64_t plane_stride, int64_t n_pixels,
+                  const double *d_axis, int g, double *d_grids, rti_stream_t stream);
+
+/* prepare_images_data on arbitrary input (analysis.py:400-409): d_grids float64
+ * [n_pixels][g][g] -> d_table int32 [g][g][image_stride], truncating toward zero;
+ * d_bad counts tiles holding NaN/inf/out-of-int32 values (reference: ValueError /
+ * OverflowError at :407).  At most 65535*32 pixels per call. */
+int rti_grids_to_table(const double *d_grids, int64_t n_pixels, int g,
+                       int32_t *d_table, int64_t image_stride, int32_t *d_bad, rti_stream_t stream);
+
+/* ---- (3) linear RBF: _interpolate_RBF analysis.py:249-260 -> scipy Rbf('linear') --
+ * Per pixel: A[j][k] = ||n_j - n_k||_2 over the pixel's n nodes (lx, ly cast to
+ * fp64), weights w = solve(A, intensity).  The kernel eliminates node 0 to get
+ * the (n-1)x(n-1) symmetric positive definite matrix
+ * B[j][k] = |n_j-n_0| + |n_k-n_0| - |n_j-n_k| and Cholesky-factorises it in fp64
+ * (no pivoting needed), which yields the same w.  d_work: scratch of
+ * rti_rbf_workspace_bytes(n, batch) bytes; pixels are processed `batch` at a
+ * time.  d_weights: float64 [n_pixels][n].  d_bad counts singular pixels
+ * (duplicate nodes; scipy raises LinAlgError). */
+int64_t rti_rbf_workspace_bytes(int n, int batch);
+int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten,
+                    int64_t n_pixels, int n, double *d_weights,
+                    void *d_work, int64_t work_bytes, int batch,
+                    int32_t *d_bad, rti_stream_t stream);
+/* Rbf.__call__ on the grid: value(v,u) = sum_k ||(axis[u], axis[v]) - n_k|| w_k.
+ * Table layout / truncation / d_bad as rti_ptm_table. */
+int rti_rbf_table(const float *d_lx, const float *d_ly, const double *d_weights,
+                  int64_t n_pixels, int n, const double *d_axis, int g,
+                  int32_t *d_table, int64_t image_stride, int32_t *d_bad, rti_stream_t stream);
+/* fp64 grids, layout as rti_ptm_grids */
+int rti_rbf_grids(const float *d_lx, const float *d_ly, const double *d_weights,
+                  int64_t n_pixels, int n, const double *d_axis, int g,
+                  double *d_grids, rti_stream_t stream);
+
+/* ---- relighting: relighting_event interactive_relighting.py:25-38 -----------------
+ * Re-render one light direction (lu, lv) from the coefficient map: value =
+ * trunc(poly(lu, lv)) clamped to [0, 255] (analysis.py:404-407 +
+ * interactive_relighting.py:35-36).  d_hsv: uint8 [n_pixels][3] HSV ROI or NULL.
+ * With d_hsv the value replaces V and the pixel is converted with OpenCV's 8-bit
+ * COLOR_HSV2BGR arithmetic into d_out uint8 [n_pixels][3]; with d_hsv == NULL
+ * d_out is uint8 [n_pixels] (the V plane only). */
+int rti_relight_ptm(const double *d_coef, int64_t plane_stride, int64_t n_pixels,
+                    double lu, double lv, const uint8_t *d_hsv, uint8_t *d_out,
+                    rti_stream_t stream);
+/* same from a float32 coefficient map (24 B/pixel; the fp32 evaluation can differ
+ * from the table by 1 where the fp64 value is within ~1e-4 of an integer) */
+int rti_relight_ptm_f32(const float *d_coef, int64_t plane_stride, int64_t n_pixels,
+                        float lu, float lv, const uint8_t *d_hsv, uint8_t *d_out,
+                        rti_stream_t stream);
+/* float64 -> float32 planar coefficient copy for rti_relight_ptm_f32 */
+int rti_coef_to_f32(const double *d_coef, int64_t n_values, float *d_out, rti_stream_t stream);
+/* table lookup variant: clamp an int32 table image to [0,255] and convert */
+int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, const uint8_t *d_hsv,
+                           uint8_t *d_out, rti_stream_t stream);
+
+/* ---- host-buffer pipeline: analysis.compute() steps 2-4 for PTM ---------------------
+ * analysis.py:466-472 in one call on HOST buffers: frames uint8 [n][rows_total*cols]
+ * and cams float64 [n][3] go in, the slab [row0, row0+rows) is fitted and evaluated,
+ * and h_table int32 [g][g][rows*cols] (prepare_images_data layout) and/or h_coef
+ * float64 [6][rows*cols] come back (either may be NULL).  Row tiles are streamed:
+ * H2D of tile t+1, fit + table of tile t and D2H of tile t-1 overlap on three
+ * streams.  Uses the current device; `tile_rows` <= 0 picks a default.  Blocks
+ * until the result is in host memory. */
+int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cams, int n,
+                         int rows_total, int cols, int row0, int rows,
+                         const double *h_axis, int g,
+                         int32_t *h_table, double *h_coef, int tile_rows);
+/* release the cached device workspace / streams of rti_ptm_compute_host */
+int rti_destroy(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTI_B200_H_ */

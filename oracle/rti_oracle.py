@@ -1,0 +1,299 @@
+"""CPU oracle for the per-pixel reflectance-fitting path of Smartphone-based-RTI.
+
+TEST INFRASTRUCTURE ONLY.  Nothing under ``smartphone-based-rti_b200/`` (the
+product) may import this module; it is used by ``tests/``, by
+``__graft_entry__.smoke()`` and by the ``cpu_baseline`` / ``--impl reference``
+legs of ``bench.py`` as the checker / timed CPU arm, never as a fallback.
+
+It is a numpy (fp64) restatement of the reference's algorithm, each function
+citing the reference lines it follows (paths relative to the upstream repo):
+
+    analysis.py:196-246   compute_intensities      -> gather_soa
+    analysis.py:263-317   _interpolate_PTM         -> ptm_design / ptm_fit / ptm_grid
+    analysis.py:249-260   _interpolate_RBF         -> rbf_fit / rbf_grid
+      (scipy 1.18.1 interpolate/_rbf.py Rbf.__init__/A/__call__, function='linear';
+       third-party, not vendored by the reference, which pins no version)
+    analysis.py:321-372   interpolate_intensities  -> light_axis / interpolate
+    analysis.py:375-411   prepare_images_data      -> table_from_grids
+    interactive_relighting.py:11-39 + Utils/utilities.py:368-376
+                                                   -> cursor_to_light / light_to_index /
+                                                      clamp_values / hsv2bgr_u8
+
+Parity pin: the reference has no tests or golden vectors of its own
+(SURVEY.md section 4).  This oracle is pinned instead against outputs of the
+reference itself, produced in the build container by
+``tests/golden/make_golden.py`` (which imports the unmodified reference) and
+committed under ``tests/golden/``; ``tests/test_oracle_golden.py`` checks it.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+__all__ = [
+    "light_axis", "gather_soa", "ptm_design", "ptm_fit", "ptm_grid", "rbf_matrix",
+    "rbf_fit", "rbf_grid", "interpolate", "table_from_grids", "cursor_to_light",
+    "light_to_index", "clamp_values", "hsv2bgr_u8", "relight_from_table",
+]
+
+
+# --------------------------------------------------------------------------- grid
+def light_axis(step: float = 0.02) -> np.ndarray:
+    """One axis of the light-direction grid (analysis.py:345-347, 390-393).
+
+    ``np.mgrid[-1:1:step]`` rounded to 2 decimals; for step 0.02 this is the
+    100 values -1.00 ... 0.98.  Both grid axes use the same values (xi[0]).
+    """
+    return np.around(np.mgrid[-1:1:step], decimals=2)
+
+
+# ------------------------------------------------------------------------- gather
+def gather_soa(frames, cams, rows: int | None = None, cols: int | None = None):
+    """Light vectors and intensities per pixel and frame (analysis.py:217-232).
+
+    frames: (N, H, W) uint8, cams: (N, 3) float64 (camera position per frame).
+    For pixel p=(x, y, 0) and frame i: l = (cam_i - p) / ||cam_i - p|| in fp64;
+    l[0], l[1] are stored as float32, the intensity as int32, all with the frame
+    index fastest: arrays of shape (rows, cols, N).
+    """
+    frames = np.asarray(frames)
+    cams = np.asarray(cams, dtype=np.float64)
+    n = frames.shape[0]
+    rows = frames.shape[1] if rows is None else rows
+    cols = frames.shape[2] if cols is None else cols
+    ys = np.arange(rows, dtype=np.float64)[:, None, None]
+    xs = np.arange(cols, dtype=np.float64)[None, :, None]
+    dx = cams[None, None, :, 0] - xs                      # (1, cols, N)
+    dy = cams[None, None, :, 1] - ys                      # (rows, 1, N)
+    dz = cams[None, None, :, 2]
+    norm = np.sqrt(dx * dx + dy * dy + dz * dz)           # np.linalg.norm, analysis.py:229
+    lx = (dx / norm).astype(np.float32)                   # stored into a float32 array, :230
+    ly = (dy / norm).astype(np.float32)                   # :231
+    inten = np.ascontiguousarray(
+        np.transpose(frames[:, :rows, :cols], (1, 2, 0))).astype(np.int32)   # :232
+    assert lx.shape == (rows, cols, n)
+    return lx, ly, inten
+
+
+# ---------------------------------------------------------------------------- PTM
+def _square_like_reference(a: np.ndarray) -> np.ndarray:
+    """``lu ** 2`` as the reference evaluates it (analysis.py:285): a numpy
+    float32 SCALAR raised to the Python int 2 goes through libm ``powf``, which
+    is within 1 ulp but not correctly rounded -- about 0.07 % of values differ
+    from the float32 product ``lu * lu`` by one ulp (measured here, numpy 2.3.5 /
+    glibc).  Slow Python loop; only used to pin the oracle bit-for-bit."""
+    flat = np.asarray(a, dtype=np.float32).ravel()
+    return np.array([v ** 2 for v in flat], dtype=np.float32).reshape(np.shape(a))
+
+
+def ptm_design(lx, ly, libm_pow: bool = False) -> np.ndarray:
+    """N x 6 design matrix (analysis.py:282-290).
+
+    lx, ly are float32; the three products are formed in float32 (numpy float32
+    scalars stay float32 under ``**2`` and ``*``) and only then promoted to fp64
+    by ``np.array`` because the row also holds the Python float ``1.``.
+
+    libm_pow=False forms the squares as correctly rounded float32 products (what
+    the CUDA path computes); libm_pow=True reproduces the reference's scalar
+    ``** 2`` bit for bit (see _square_like_reference).  The two differ by one
+    float32 ulp in ~0.07 % of entries, i.e. ~4e-8 relative in the coefficients.
+    """
+    lu = np.asarray(lx, dtype=np.float32)
+    lv = np.asarray(ly, dtype=np.float32)
+    m = np.empty(lu.shape + (6,), dtype=np.float64)
+    m[..., 0] = _square_like_reference(lu) if libm_pow else lu * lu
+    m[..., 1] = _square_like_reference(lv) if libm_pow else lv * lv
+    m[..., 2] = lu * lv
+    m[..., 3] = lu
+    m[..., 4] = lv
+    m[..., 5] = 1.0
+    return m
+
+
+def ptm_fit(lx, ly, values, libm_pow: bool = False) -> np.ndarray:
+    """Six biquadratic coefficients of one pixel (analysis.py:295-298).
+
+    Full SVD of the design matrix, ``a = V^T.T @ ((U.T @ L)[:6] / s)``: the
+    minimum-norm least-squares solution without a rank cut-off.  N < 6 raises
+    ValueError exactly like the reference (shapes not aligned in the last dot).
+    """
+    a_mat = ptm_design(lx, ly, libm_pow)
+    rhs = np.asarray(values)
+    u, s, vt = np.linalg.svd(a_mat)
+    c = np.dot(u.T, rhs)
+    w = np.divide(c[:len(s)], s)
+    return np.dot(vt.T, w)
+
+
+def ptm_fit_batch(lx, ly, values) -> np.ndarray:
+    """ptm_fit over leading axes (same algorithm, reduced SVD, batched)."""
+    a_mat = ptm_design(lx, ly)                                    # (..., N, 6)
+    rhs = np.asarray(values, dtype=np.float64)[..., None]          # (..., N, 1)
+    if a_mat.shape[-2] < 6:
+        raise ValueError("PTM fit needs at least 6 light samples")
+    u, s, vt = np.linalg.svd(a_mat, full_matrices=False)
+    c = np.matmul(np.swapaxes(u, -1, -2), rhs)[..., 0]            # (..., 6)
+    return np.matmul(np.swapaxes(vt, -1, -2), (c / s)[..., None])[..., 0]
+
+
+def ptm_grid(coef, axis) -> np.ndarray:
+    """Evaluate the biquadratic on the grid (analysis.py:301-315).
+
+    Returns (G, G) fp64 indexed [v(ly)][u(lx)]; the sum is formed left to right
+    exactly as the reference does so the fp64 result is bit-identical.
+    """
+    a = np.asarray(coef, dtype=np.float64)
+    ax = np.asarray(axis, dtype=np.float64)
+    lu = ax[None, :]
+    lv = ax[:, None]
+    out = a[..., 0, None, None] * (lu ** 2)
+    out = out + a[..., 1, None, None] * (lv ** 2)
+    out = out + a[..., 2, None, None] * (lu * lv)
+    out = out + a[..., 3, None, None] * lu
+    out = out + a[..., 4, None, None] * lv
+    out = out + a[..., 5, None, None]
+    return out
+
+
+# ---------------------------------------------------------------------------- RBF
+def rbf_matrix(lx, ly) -> np.ndarray:
+    """Kernel matrix of scipy's legacy ``Rbf(function='linear')``.
+
+    A[j, k] = ||n_j - n_k||_2 with nodes cast to fp64 (scipy _rbf.py Rbf.A:
+    squareform(pdist(xi.T)); 'linear' is phi(r) = r; smooth = 0).
+    """
+    x = np.asarray(lx, dtype=np.float64)
+    y = np.asarray(ly, dtype=np.float64)
+    ddx = x[..., :, None] - x[..., None, :]
+    ddy = y[..., :, None] - y[..., None, :]
+    return np.sqrt(ddx * ddx + ddy * ddy)
+
+
+def rbf_fit(lx, ly, values) -> np.ndarray:
+    """RBF weights of one pixel: solve(A, d) (scipy _rbf.py Rbf.__init__).
+
+    Duplicate nodes make A singular and raise numpy's LinAlgError like
+    scipy.linalg.solve does in the reference.
+    """
+    a_mat = rbf_matrix(lx, ly)
+    d = np.asarray(values, dtype=np.float64)
+    return np.linalg.solve(a_mat, d[..., None])[..., 0]
+
+
+def rbf_grid(lx, ly, weights, axis) -> np.ndarray:
+    """Evaluate the interpolant on the grid (scipy _rbf.py Rbf.__call__).
+
+    out[v, u] = sum_k ||(axis[u], axis[v]) - n_k|| * w_k, (G, G) fp64 indexed
+    [ly][lx] (analysis.py:345, 361-363: x_fine = xi, y_fine = yi of the mgrid).
+    """
+    x = np.asarray(lx, dtype=np.float64)
+    y = np.asarray(ly, dtype=np.float64)
+    w = np.asarray(weights, dtype=np.float64)
+    ax = np.asarray(axis, dtype=np.float64)
+    gx = ax[None, :, None]
+    gy = ax[:, None, None]
+    r = np.sqrt((gx - x[None, None, :]) ** 2 + (gy - y[None, None, :]) ** 2)
+    return r @ w
+
+
+# ------------------------------------------------------------------------- driver
+def interpolate(lx, ly, inten, ptm: bool, step: float = 0.02,
+                libm_pow: bool = False) -> np.ndarray:
+    """interpolate_intensities as one array (analysis.py:321-372).
+
+    Returns (rows, cols, G, G) fp64: [y][x][ly][lx].
+    """
+    ax = light_axis(step)
+    rows, cols, _ = lx.shape
+    out = np.empty((rows, cols, ax.size, ax.size), dtype=np.float64)
+    for y in range(rows):
+        for x in range(cols):
+            if ptm:
+                out[y, x] = ptm_grid(ptm_fit(lx[y, x], ly[y, x], inten[y, x], libm_pow), ax)
+            else:
+                out[y, x] = rbf_grid(lx[y, x], ly[y, x],
+                                     rbf_fit(lx[y, x], ly[y, x], inten[y, x]), ax)
+    return out
+
+
+def table_from_grids(grids) -> np.ndarray:
+    """prepare_images_data (analysis.py:400-409).
+
+    (rows, cols, G, G) fp64 -> (G, G, rows, cols) int32: table[ly][lx][y][x].
+    Element assignment of a Python float into an int32 array truncates toward
+    zero and raises on NaN / inf / out-of-range values; so does this.
+    """
+    g = np.asarray(grids, dtype=np.float64)
+    if not np.all(np.isfinite(g)):
+        raise ValueError("cannot convert float NaN/inf to integer")
+    if np.any(np.abs(g) >= 2147483648.0):
+        raise OverflowError("Python integer out of bounds for int32")
+    return np.ascontiguousarray(np.transpose(np.trunc(g), (2, 3, 0, 1))).astype(np.int32)
+
+
+# ---------------------------------------------------------------------- relighting
+def cursor_to_light(x: int, y: int, h: int, w: int):
+    """Mouse position -> (lx, ly) (Utils/utilities.py:368-376)."""
+    lx = round(2 * (x / w) - 1, 2)
+    ly = round(2 * (y / h) - 1, 2)
+    if lx >= 0.99:
+        lx = 0.98
+    if ly >= 0.99:
+        ly = 0.98
+    return lx, ly
+
+
+def light_to_index(l: float) -> int:
+    """(lx or ly) -> table index (interactive_relighting.py:25-26); Python
+    round() is round-half-even."""
+    return round((1 + l) / 2 * 100)
+
+
+def clamp_values(img) -> np.ndarray:
+    """values[values > 255] = 255; values[values <= 0] = 0
+    (interactive_relighting.py:35-36), out of place here."""
+    return np.clip(np.asarray(img), 0, 255)
+
+
+def hsv2bgr_u8(hsv) -> np.ndarray:
+    """8-bit HSV -> BGR with OpenCV's cv2.COLOR_HSV2BGR semantics
+    (interactive_relighting.py:38): H in [0,180), S and V in [0,255].
+
+    OpenCV is third-party to the reference (no version pinned; 4.13.0 in the
+    build container).  This restates what its vectorised 8-bit kernel computes,
+    established by exhaustive comparison over all 180*256*256 inputs
+    (tests/golden/make_golden.py, 0 mismatches): h' = H*(6/180), sector =
+    trunc(h'), f = h' - sector, s = S/255, v = V/255 in float32,
+        p = v*(1 - s), q = v*fma(-s, f, 1), t = v*fma(-s, 1 - f, 1),
+    channel = TRUNCATE(x * 255).  (OpenCV's scalar tail, used for the last
+    < 64 pixels of a buffer, rounds instead of truncating; callers comparing
+    against cv2 on arbitrary images must allow 1 LSB there.)
+    """
+    hsv = np.asarray(hsv, dtype=np.uint8)
+    f32 = np.float32
+    h = hsv[..., 0].astype(f32) * f32(6.0 / 180.0)
+    s = hsv[..., 1].astype(f32) * f32(1.0 / 255.0)
+    v = hsv[..., 2].astype(f32) * f32(1.0 / 255.0)
+    sector = np.trunc(h).astype(np.int32)
+    f = h - sector.astype(f32)
+    sector = sector % 6
+    one = f32(1.0)
+
+    def fma(a, b, c):          # single-rounded a*b+c (exact in fp64 for these magnitudes)
+        return (a.astype(np.float64) * b.astype(np.float64) + np.float64(c)).astype(f32)
+
+    t1 = v * (one - s)
+    t2 = v * fma(-s, f, one)
+    t3 = v * fma(-s, one - f, one)
+    tab = np.stack([v, t1, t2, t3], axis=-1)
+    sel = np.array([[1, 3, 0], [1, 0, 2], [3, 0, 1], [0, 2, 1], [0, 1, 3], [2, 1, 0]])
+    bgr = np.take_along_axis(tab, sel[sector], axis=-1)   # b, g, r table slots
+    return np.clip(np.trunc(bgr * f32(255.0)), 0, 255).astype(np.uint8)
+
+
+def relight_from_table(table, hsv_roi, lx: float, ly: float) -> np.ndarray:
+    """relighting_event (interactive_relighting.py:25-38) without the window:
+    look the image up, clamp, write it into V, convert HSV -> BGR."""
+    values = clamp_values(table[light_to_index(ly)][light_to_index(lx)])
+    img = np.array(hsv_roi, dtype=np.uint8, copy=True)
+    img[:, :, 2] = values
+    return hsv2bgr_u8(img)

@@ -1,0 +1,461 @@
+"""Host-side mirror of the reference's analysis.py call surface for the per-pixel
+reflectance fitting path, running on librti_b200.so (hand-written sm_100a CUDA).
+
+Same names, arguments, defaults, error messages and return shapes as the
+reference (citations are into the upstream repo):
+
+    compute_intensities(data, first_only=False)                      analysis.py:196-246
+    interpolate_intensities(data, interpolate_PTM=False, first_only=False)   :321-372
+    prepare_images_data(data, first_only=False)                      :375-411
+    compute(video_name, from_storage, storage_filepath, interpolate_PTM,
+            notification_email, debug)                               :414-482
+
+``install(analysis_module)`` rebinds the first three inside the reference's own
+module so that its unmodified ``compute()`` runs on the GPU.
+
+Return objects index like the reference's but stay on the device until touched:
+the reference's dense returns are 12 B per pixel.light and 80 kB per pixel, which
+do not scale.  PyTorch is used only for device memory, streams
+and (in sharding.py) torch.distributed; all arithmetic is in the CUDA library.
+There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+
+from . import _capi
+from . import constants as _default_constants
+
+_cst = _default_constants           # rebound by install() to the reference's constants module
+
+
+def _torch():
+    import torch
+    if not torch.cuda.is_available():
+        raise RuntimeError("smartphone-based-rti_b200 needs a CUDA device (sm_100a); no CPU fallback")
+    return torch
+
+
+def _stream_ptr(torch):
+    return torch.cuda.current_stream().cuda_stream
+
+
+def light_axis(step=None) -> np.ndarray:
+    """One axis of the light grid: np.around(np.mgrid[-1:1:step], 2) (analysis.py:345-347)."""
+    step = _cst.INTERPOLATION_PARAM if step is None else step
+    return np.around(np.mgrid[-1:1:step], decimals=2)
+
+
+# --------------------------------------------------------------------------- records
+def _stack_frames(data, rows, cols):
+    """list[(uint8 (H,W), float64 (3,))] -> contiguous (N, rows, cols) uint8 + (N, 3) float64."""
+    n = len(data)
+    frames = np.empty((n, rows, cols), dtype=np.uint8)
+    cams = np.empty((n, 3), dtype=np.float64)
+    for i, rec in enumerate(data):
+        roi = np.asarray(rec[0])
+        if roi.ndim != 2 or roi.shape[0] < rows or roi.shape[1] < cols:
+            # the reference raises IndexError at intensities[y][x] (analysis.py:232)
+            raise IndexError("frame %d ROI has shape %s, need at least (%d, %d)" % (i, roi.shape, rows, cols))
+        frames[i] = roi[:rows, :cols]
+        cams[i] = np.asarray(rec[1], dtype=np.float64).reshape(3)
+    return frames, cams
+
+
+class FrameStack:
+    """Device-resident frame records: uint8 (N, rows, cols) + float64 (N, 3), plus the
+    global row of the slab's first row (row0) for row-tile sharding."""
+
+    def __init__(self, frames, cams, row0=0):
+        torch = _torch()
+        frames = np.ascontiguousarray(frames, dtype=np.uint8)
+        cams = np.ascontiguousarray(cams, dtype=np.float64)
+        self.n, self.rows, self.cols = frames.shape
+        self.row0 = int(row0)
+        self.d_frames = torch.from_numpy(frames).cuda(non_blocking=False)
+        self.d_cams = torch.from_numpy(cams).cuda()
+
+    @classmethod
+    def from_device(cls, d_frames, d_cams, row0=0):
+        self = cls.__new__(cls)
+        self.n, self.rows, self.cols = d_frames.shape
+        self.row0 = int(row0)
+        self.d_frames, self.d_cams = d_frames.contiguous(), d_cams.contiguous()
+        return self
+
+    @property
+    def n_pixels(self):
+        return self.rows * self.cols
+
+
+class _SoA:
+    """The three (rows, cols, N) arrays of compute_intensities on the device, produced
+    on first use by the gather kernel."""
+
+    def __init__(self, stack: FrameStack):
+        self.stack = stack
+        self._arrays = None
+
+    def device_arrays(self):
+        if self._arrays is None:
+            torch = _torch()
+            s = self.stack
+            shape = (s.n_pixels, s.n)
+            lx = torch.empty(shape, dtype=torch.float32, device="cuda")
+            ly = torch.empty(shape, dtype=torch.float32, device="cuda")
+            inten = torch.empty(shape, dtype=torch.int32, device="cuda")
+            _capi.call("rti_gather_soa", s.d_frames.data_ptr(), s.rows * s.cols, s.d_cams.data_ptr(),
+                       s.n, s.row0, s.rows, s.cols, lx.data_ptr(), ly.data_ptr(), inten.data_ptr(),
+                       _stream_ptr(torch))
+            self._arrays = (lx, ly, inten)
+        return self._arrays
+
+
+class DeviceArrayView:
+    """One of pixels_lx / pixels_ly / pixels_intensity: indexes and converts like the
+    (rows, cols, N) ndarray the reference returns (analysis.py:217-219, 245)."""
+
+    def __init__(self, soa: _SoA, which: int):
+        self._soa, self._which = soa, which
+        s = soa.stack
+        self.shape = (s.rows, s.cols, s.n)
+        self.dtype = np.dtype(np.int32 if which == 2 else np.float32)
+        self.ndim = 3
+
+    def __len__(self):
+        return self.shape[0]
+
+    def device(self):
+        return self._soa.device_arrays()[self._which].view(self.shape)
+
+    def __array__(self, dtype=None, copy=None):
+        a = self.device().cpu().numpy()
+        return a if dtype is None else a.astype(dtype)
+
+    def __getitem__(self, idx):
+        out = self.device()[idx]
+        return out.cpu().numpy() if out.ndim else out.item()
+
+
+def compute_intensities(data, first_only=False):
+    """Compute light vectors intensities foreach frame pixel (analysis.py:196-246).
+
+    :param data: list of (intensities uint8 (R,R), camera_position float64 (3,)) per frame
+    :param first_only: only pixel (0, 0)
+    :return: (pixels_lx, pixels_ly, pixels_intensity), each indexable [y][x][i]
+    """
+    if data is None or len(data) <= 0:
+        raise Exception("Error computing intensities: results are empty")
+    print("Computing intensities values:")
+    range_val = 1 if first_only else _cst.ROI_DIAMETER
+    frames, cams = _stack_frames(data, range_val, range_val)
+    soa = _SoA(FrameStack(frames, cams))
+    return (DeviceArrayView(soa, 0), DeviceArrayView(soa, 1), DeviceArrayView(soa, 2))
+
+
+# --------------------------------------------------------------------- interpolation
+class InterpolationResult:
+    """interpolated_intensities[y][x] -> (G, G) float64 indexed [ly][lx]
+    (analysis.py:349, 372), backed by the per-pixel model on the device:
+    PTM: coefficient map float64 (6, P);  RBF: nodes (lx, ly) and weights float64 (P, N).
+    A pixel's grid is evaluated on demand."""
+
+    def __init__(self, mode, rows, cols, axis, coef=None, lx=None, ly=None, weights=None, row0=0):
+        self.mode, self.rows, self.cols, self.row0 = mode, rows, cols, row0
+        self.axis = np.ascontiguousarray(axis, dtype=np.float64)
+        self.coef, self.lx, self.ly, self.weights = coef, lx, ly, weights
+        self._d_axis = None
+
+    @property
+    def n_pixels(self):
+        return self.rows * self.cols
+
+    def d_axis(self):
+        if self._d_axis is None:
+            self._d_axis = _torch().from_numpy(self.axis).cuda()
+        return self._d_axis
+
+    def __len__(self):
+        return self.rows
+
+    def __getitem__(self, y):
+        if not -self.rows <= y < self.rows:
+            raise IndexError("list index out of range")
+        return _ResultRow(self, y % self.rows)
+
+    def grids(self, p0, count):
+        """float64 (count, G, G) grids of pixels [p0, p0 + count)."""
+        torch = _torch()
+        g = self.axis.size
+        out = torch.empty((count, g, g), dtype=torch.float64, device="cuda")
+        if self.mode == "ptm":
+            _capi.call("rti_ptm_grids", self.coef.data_ptr() + 8 * p0, self.n_pixels, count,
+                       self.d_axis().data_ptr(), g, out.data_ptr(), _stream_ptr(torch))
+        else:
+            n = self.weights.shape[1]
+            _capi.call("rti_rbf_grids", self.lx.data_ptr() + 4 * p0 * n, self.ly.data_ptr() + 4 * p0 * n,
+                       self.weights.data_ptr() + 8 * p0 * n, count, n, self.d_axis().data_ptr(), g,
+                       out.data_ptr(), _stream_ptr(torch))
+        return out.cpu().numpy()
+
+    def coefficients(self) -> np.ndarray:
+        """PTM only: (6, rows, cols) float64 a_matrix per pixel (analysis.py:298)."""
+        if self.mode != "ptm":
+            raise ValueError("coefficients() is defined for PTM results")
+        return self.coef.cpu().numpy().reshape(6, self.rows, self.cols)
+
+    def to_list(self):
+        """Materialise the reference's nested list (80 kB per pixel!)."""
+        out = []
+        for y in range(self.rows):
+            g = self.grids(y * self.cols, self.cols)
+            out.append([g[x] for x in range(self.cols)])
+        return out
+
+
+class _ResultRow:
+    def __init__(self, res, y):
+        self._res, self._y = res, y
+
+    def __len__(self):
+        return self._res.cols
+
+    def __getitem__(self, x):
+        cols = self._res.cols
+        if not -cols <= x < cols:
+            raise IndexError("list index out of range")
+        return self._res.grids(self._y * cols + x % cols, 1)[0]
+
+
+def _fit_ptm_from_stack(stack: FrameStack):
+    torch = _torch()
+    coef = torch.empty((6, stack.n_pixels), dtype=torch.float64, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_frames", stack.d_frames.data_ptr(), stack.rows * stack.cols,
+               stack.d_cams.data_ptr(), stack.n, stack.row0, stack.rows, stack.cols,
+               coef.data_ptr(), stack.n_pixels, bad.data_ptr(), _stream_ptr(torch))
+    return coef, bad
+
+
+def _as_device_soa(data, range_val):
+    """(lx, ly, inten) as device (P, N) tensors restricted to [range_val, range_val]."""
+    torch = _torch()
+    if all(isinstance(a, DeviceArrayView) for a in data) and data[0].shape[:2] == (range_val, range_val):
+        return data[0]._soa.device_arrays()
+    out = []
+    for a, dt in zip(data, (np.float32, np.float32, np.int32)):
+        arr = np.asarray(a)
+        if arr.ndim != 3 or arr.shape[0] < range_val or arr.shape[1] < range_val:
+            raise IndexError("pixel data of shape %s does not cover a %dx%d ROI" % (arr.shape, range_val, range_val))
+        arr = np.ascontiguousarray(arr[:range_val, :range_val], dtype=dt)
+        out.append(torch.from_numpy(arr).cuda().view(range_val * range_val, arr.shape[2]))
+    return tuple(out)
+
+
+def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
+    """Interpolate pixel intensities (analysis.py:321-372).
+
+    :param data: (pixels_lx, pixels_ly, pixels_intensity) as returned by compute_intensities
+                 (device views) or as plain (R, R, N) ndarrays
+    :param interpolate_PTM: PTM if True, else linear RBF
+    :param first_only: only pixel (0, 0)
+    :return: interpolated_intensities[y][x][ly][lx] => intensity (lazy, see InterpolationResult)
+    """
+    if data is None or len(data) != 3:
+        raise Exception("Error computing interpolation: results are empty or invalid")
+    print("Computing interpolation values:")
+    torch = _torch()
+    range_val = 1 if first_only else _cst.ROI_DIAMETER
+    axis = light_axis()
+
+    fused = (interpolate_PTM and all(isinstance(a, DeviceArrayView) for a in data)
+             and data[0]._soa is data[1]._soa is data[2]._soa
+             and data[0].shape[:2] == (range_val, range_val))
+    if fused:
+        stack = data[0]._soa.stack
+        coef, bad = _fit_ptm_from_stack(stack)
+        _raise_if_bad(bad, "PTM")
+        return InterpolationResult("ptm", range_val, range_val, axis, coef=coef, row0=stack.row0)
+
+    lx, ly, inten = _as_device_soa(data, range_val)
+    n_pixels, n = lx.shape
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    if interpolate_PTM:
+        coef = torch.empty((6, n_pixels), dtype=torch.float64, device="cuda")
+        _capi.call("rti_ptm_fit_soa", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), n_pixels, n,
+                   coef.data_ptr(), n_pixels, bad.data_ptr(), _stream_ptr(torch))
+        _raise_if_bad(bad, "PTM")
+        return InterpolationResult("ptm", range_val, range_val, axis, coef=coef)
+    weights = rbf_fit_device(lx, ly, inten, bad)
+    _raise_if_bad(bad, "RBF")
+    return InterpolationResult("rbf", range_val, range_val, axis, lx=lx, ly=ly, weights=weights)
+
+
+def rbf_fit_device(lx, ly, inten, bad):
+    """Linear-RBF weights (P, N) float64 for device SoA tensors (scipy Rbf.__init__)."""
+    torch = _torch()
+    n_pixels, n = lx.shape
+    weights = torch.empty((n_pixels, n), dtype=torch.float64, device="cuda")
+    free, _total = torch.cuda.mem_get_info()
+    lib = _capi.load()
+    per_pixel = max(1, lib.rti_rbf_workspace_bytes(n, 1))
+    batch = int(max(1, min(n_pixels, (free // 2) // per_pixel, 148 * 64)))
+    work_bytes = lib.rti_rbf_workspace_bytes(n, batch)
+    work = torch.empty(max(work_bytes, 8), dtype=torch.uint8, device="cuda")
+    _capi.call("rti_rbf_fit_soa", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), n_pixels, n,
+               weights.data_ptr(), work.data_ptr(), work_bytes, batch, bad.data_ptr(), _stream_ptr(torch))
+    return weights
+
+
+def _raise_if_bad(bad, what):
+    count = int(bad.item())          # synchronises: numerical failures surface here
+    if count > 0:
+        raise _capi.RtiSingularError(_capi.RTI_ERR_SINGULAR,
+                                     "%s: %d pixel(s) have a singular system" % (what, count))
+
+
+# ----------------------------------------------------------------------------- table
+def table_device(res: InterpolationResult, out=None):
+    """int32 (G, G, P) table of a result on the device (prepare_images_data layout)."""
+    torch = _torch()
+    g = res.axis.size
+    p = res.n_pixels
+    if out is None:
+        out = torch.empty((g, g, p), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    if res.mode == "ptm":
+        _capi.call("rti_ptm_table", res.coef.data_ptr(), p, p, res.d_axis().data_ptr(), g,
+                   out.data_ptr(), p, bad.data_ptr(), _stream_ptr(torch))
+    else:
+        n = res.weights.shape[1]
+        _capi.call("rti_rbf_table", res.lx.data_ptr(), res.ly.data_ptr(), res.weights.data_ptr(), p, n,
+                   res.d_axis().data_ptr(), g, out.data_ptr(), p, bad.data_ptr(), _stream_ptr(torch))
+    if int(bad.item()) > 0:
+        # analysis.py:407 raises ValueError (NaN/inf) or OverflowError (out of int32 range)
+        raise ValueError("cannot convert interpolated values to int32 (NaN, inf or out of range)")
+    return out
+
+
+def prepare_images_data(data, first_only=False):
+    """Prepare images for each light position (analysis.py:375-411).
+
+    :param data: the object returned by interpolate_intensities (or the reference's nested
+                 list interpolation_intensities[y][x][ly][lx])
+    :return: interpolated_images[ly][lx] -> writable int32 (R, R) ndarray
+    """
+    if data is None or len(data) <= 0:
+        raise Exception("Error preparing images: results are empty")
+    print("Preparing images values:")
+    torch = _torch()
+    range_val = 1 if first_only else _cst.ROI_DIAMETER
+    if isinstance(data, InterpolationResult):
+        if (data.rows, data.cols) != (range_val, range_val):
+            raise IndexError("interpolation result is %dx%d, ROI is %d" % (data.rows, data.cols, range_val))
+        g = data.axis.size
+        table = table_device(data).cpu().numpy().reshape(g, g, range_val, range_val)
+    else:
+        # plain nested list / array [y][x][ly][lx]: transpose + truncate on the device
+        grids = np.ascontiguousarray(
+            np.asarray([[np.asarray(data[y][x], dtype=np.float64) for x in range(range_val)]
+                        for y in range(range_val)]))
+        g = grids.shape[-1]
+        p = range_val * range_val
+        d_grids = torch.from_numpy(grids).cuda()
+        d_table = torch.empty((g, g, p), dtype=torch.int32, device="cuda")
+        bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+        step = 65535 * 32
+        for p0 in range(0, p, step):
+            cnt = min(step, p - p0)
+            _capi.call("rti_grids_to_table", d_grids.data_ptr() + 8 * p0 * g * g, cnt, g,
+                       d_table.data_ptr() + 4 * p0, p, bad.data_ptr(), _stream_ptr(torch))
+        if int(bad.item()) > 0:
+            raise ValueError("cannot convert interpolated values to int32 (NaN, inf or out of range)")
+        table = d_table.cpu().numpy().reshape(g, g, range_val, range_val)
+    return [[table[v, u] for u in range(table.shape[1])] for v in range(table.shape[0])]
+
+
+# ------------------------------------------------------------------------- file I/O
+def write_on_file(data, filename, compressed=True):
+    """Same files as Utils/utilities.py:48-70: '<name>.pbz2' (bz2 + pickle) or '<name>.pickle'."""
+    import bz2
+    import pickle
+    print("Writing on file {}".format(filename))
+    if compressed:
+        filename = filename + ".pbz2"
+        with bz2.BZ2File(filename, "wb") as f:
+            pickle.dump(data, f)
+    else:
+        filename = filename + ".pickle"
+        with open(filename, "wb") as f:
+            pickle.dump(data, f)
+    print("Saved file {}".format(filename))
+
+
+def read_from_file(filename, compressed=True):
+    """Utils/utilities.py:73-101, including its 'Storage file not found!' error."""
+    import bz2
+    import pickle
+    filename = filename + (".pbz2" if compressed else ".pickle")
+    if not os.path.isfile(filename):
+        raise Exception("Storage file not found!")
+    print("Reading from file {}".format(filename))
+    opener = bz2.BZ2File if compressed else open
+    with opener(filename, "rb") as f:
+        return pickle.load(f)
+
+
+def compute(video_name="coin1", from_storage=False, storage_filepath=None, interpolate_PTM=False,
+            notification_email=False, debug=False):
+    """Main function (analysis.py:414-482), steps 2-4 on the GPU.
+
+    Step 1 from video (from_storage=False) is the reference's acquisition stage and is
+    not part of this package.  notification_email is accepted for signature
+    compatibility and never sends anything.
+    """
+    results_frames_filepath = "assets/frames_results_{}".format(video_name)
+    results_interpolation_filepath = "assets/interpolation_results_{}".format(video_name)
+    print("\nStep 1: Computing frames values")
+    if from_storage is True:
+        if storage_filepath is not None:
+            results_frames_filepath = storage_filepath
+        results_frames = read_from_file(results_frames_filepath)
+    else:
+        raise NotImplementedError(
+            "video acquisition (analysis.py:436-460) is outside this package; run the reference's "
+            "acquisition once and call compute(from_storage=True)")
+    if debug:
+        print("Notice: computing in debug mode (first pixel only)")
+    print("\nStep 2: Computing pixels intensities")
+    data = compute_intensities(results_frames, first_only=debug)
+    print("\nStep 3: Computing interpolation")
+    results_interpolation = interpolate_intensities(data, interpolate_PTM=interpolate_PTM, first_only=debug)
+    print("\nStep 4: Preparing images data")
+    results_images = prepare_images_data(results_interpolation, first_only=debug)
+    if debug is False:
+        write_on_file(results_images, results_interpolation_filepath, compressed=False)
+        if notification_email:
+            print("notification_email is ignored (no network side effects)")
+    print("\nOK. Computation completed")
+    return results_images
+
+
+def install(analysis_module, constants_module=None):
+    """Drop-in: rebind the reference module's hot functions to this implementation.
+
+    analysis.compute() resolves compute_intensities / interpolate_intensities /
+    prepare_images_data through its module globals at call time (analysis.py:466-472), so
+    after ``install(analysis)`` the unmodified reference ``compute()`` runs on the GPU.
+    The tunables are then read from the reference's own ``constants`` module.
+    """
+    global _cst
+    if constants_module is None:
+        constants_module = getattr(analysis_module, "cst", None) or sys.modules.get("constants")
+    if constants_module is not None:
+        _cst = constants_module
+    analysis_module.compute_intensities = compute_intensities
+    analysis_module.interpolate_intensities = interpolate_intensities
+    analysis_module.prepare_images_data = prepare_images_data
+    return analysis_module

@@ -1,0 +1,71 @@
+"""Row-tile sharding of the pixel domain across the GPUs of one box.
+
+Every pixel's gather, fit and evaluation is independent (analysis.py:221-232, 350-363),
+so the ROI is cut into contiguous row slabs, one per rank, with NO collective on the hot
+path.  Pixel coordinates stay global (row0 + local row) because p = (x, y, 0) enters the
+light vector.  The only communication is the final gather of the small per-pixel model
+(PTM coefficients: 48 B/pixel) to one rank; the int32 tables stay sharded.
+
+One process per GPU, launched by torchrun; torch.distributed (NCCL on GPUs, gloo in the
+CPU tests) is plumbing only.
+"""
+from __future__ import annotations
+
+
+def row_partition(rows: int, world_size: int):
+    """[(row0, n_rows)] per rank: rows // world_size each, the remainder spread one row at
+    a time over the LAST ranks (so rank 0, which also gathers, never has the extra row)."""
+    if rows < 0 or world_size <= 0:
+        raise ValueError("rows >= 0 and world_size > 0 required")
+    base, rem = divmod(rows, world_size)
+    out, r0 = [], 0
+    for r in range(world_size):
+        n = base + (1 if r >= world_size - rem else 0)
+        out.append((r0, n))
+        r0 += n
+    return out
+
+
+def gather_planar(local, rows_total: int, cols: int, dst: int = 0, group=None):
+    """Gather per-rank planar maps (K, rows_r * cols) into (K, rows_total, cols) on `dst`.
+
+    `local` is this rank's tensor for its row_partition() slab (any K, any dtype, CPU or
+    CUDA).  Point-to-point sends (uneven slabs need no padding); returns the assembled
+    tensor on `dst` and None elsewhere.
+    """
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    parts = row_partition(rows_total, world)
+    k = local.shape[0]
+    r0, nr = parts[rank]
+    if local.shape != (k, nr * cols):
+        raise ValueError("rank %d: expected local shape %s, got %s" % (rank, (k, nr * cols), tuple(local.shape)))
+    if rank != dst:
+        if nr > 0:
+            dist.send(local.contiguous(), dst=dst, group=group)
+        return None
+    full = torch.empty((k, rows_total, cols), dtype=local.dtype, device=local.device)
+    for src, (s0, sn) in enumerate(parts):
+        if sn == 0:
+            continue
+        if src == dst:
+            full[:, s0:s0 + sn, :] = local.view(k, sn, cols)
+        else:
+            buf = torch.empty((k, sn * cols), dtype=local.dtype, device=local.device)
+            dist.recv(buf, src=src, group=group)
+            full[:, s0:s0 + sn, :] = buf.view(k, sn, cols)
+    return full
+
+
+def fit_ptm_slab(frames_slab, cams, row0: int):
+    """This rank's share of the PTM fit: frames_slab uint8 (N, rows_r, cols) holding ROI rows
+    [row0, row0 + rows_r), cams float64 (N, 3).  Returns the device InterpolationResult."""
+    from . import analysis as A
+
+    stack = A.FrameStack(frames_slab, cams, row0=row0)
+    coef, bad = A._fit_ptm_from_stack(stack)
+    A._raise_if_bad(bad, "PTM")
+    return A.InterpolationResult("ptm", stack.rows, stack.cols, A.light_axis(), coef=coef, row0=row0)

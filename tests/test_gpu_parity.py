@@ -1,0 +1,455 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle and the committed
+reference outputs.  Integer/index work is bit-exact; floating point tolerances are the
+ones BASELINE.json's north_star states (PTM coefficients / relit values 1e-4 relative vs
+fp64, lx/ly <= 1 ulp of float32) -- the fp64 kernels are in fact held to far tighter
+bounds below."""
+import numpy as np
+import pytest
+
+import rti_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+PTM_COEF_RTOL = 1e-9        # achieved (fp64 normal equations); north_star allows 1e-4
+LIGHT_ULP = 1               # float32 ulps on lx / ly
+
+
+@pytest.fixture(scope="module")
+def torch_cuda(lib):
+    import torch
+    assert torch.cuda.is_available()
+    torch.cuda.set_device(0)
+    return torch
+
+
+def ulp_diff(a, b):
+    return np.abs(a.view(np.int32).astype(np.int64) - b.view(np.int32).astype(np.int64))
+
+
+def dev(torch, a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def gpu_gather(torch, frames, cams, row0=0):
+    from rti_b200 import _capi
+    n, rows, cols = frames.shape
+    d_f, d_c = dev(torch, frames), dev(torch, cams)
+    lx = torch.empty((rows * cols, n), dtype=torch.float32, device="cuda")
+    ly = torch.empty_like(lx)
+    inten = torch.empty((rows * cols, n), dtype=torch.int32, device="cuda")
+    _capi.call("rti_gather_soa", d_f.data_ptr(), rows * cols, d_c.data_ptr(), n, row0, rows, cols,
+               lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), None)
+    torch.cuda.synchronize()
+    shape = (rows, cols, n)
+    return lx.cpu().numpy().reshape(shape), ly.cpu().numpy().reshape(shape), inten.cpu().numpy().reshape(shape)
+
+
+def gpu_fit_frames(torch, frames, cams, row0=0):
+    from rti_b200 import _capi
+    n, rows, cols = frames.shape
+    d_f, d_c = dev(torch, frames), dev(torch, cams)
+    coef = torch.empty((6, rows * cols), dtype=torch.float64, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_frames", d_f.data_ptr(), rows * cols, d_c.data_ptr(), n, row0, rows, cols,
+               coef.data_ptr(), rows * cols, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    return coef, int(bad.item())
+
+
+def coef_rel_err(coef_gpu, coef_ref):
+    """max over pixels of ||a_gpu - a_ref||_inf / ||a_ref||_inf; coef_* are (P, 6)."""
+    scale = np.max(np.abs(coef_ref), axis=1, keepdims=True)
+    return float(np.max(np.abs(coef_gpu - coef_ref) / scale))
+
+
+# ------------------------------------------------------------------------------ gather
+def test_gather_matches_reference_golden(torch_cuda, ref_small):
+    lx, ly, inten = gpu_gather(torch_cuda, ref_small["frames"], ref_small["cams"])
+    assert np.array_equal(inten, ref_small["inten"])                  # bit-exact integers
+    assert ulp_diff(lx, ref_small["lx"]).max() <= LIGHT_ULP
+    assert ulp_diff(ly, ref_small["ly"]).max() <= LIGHT_ULP
+    # in practice the fp64 evaluation rounds to the same float32 everywhere
+    assert np.count_nonzero(lx != ref_small["lx"]) + np.count_nonzero(ly != ref_small["ly"]) == 0
+
+
+@pytest.mark.parametrize("rows,cols,n,row0", [(1, 1, 1, 0), (3, 5, 7, 0), (9, 33, 130, 4), (16, 64, 256, 0),
+                                              (5, 40, 129, 11), (2, 31, 4, 0)])
+def test_gather_ragged_shapes(torch_cuda, rows, cols, n, row0):
+    from rti_b200 import synthetic
+    frames, cams = synthetic.random_stack(rows, cols, n, seed=rows * 100 + n, rows_total=rows + row0)
+    lx, ly, inten = gpu_gather(torch_cuda, frames, cams, row0=row0)
+    # oracle evaluates global rows: build the full-height problem and slice
+    full = np.zeros((n, rows + row0, cols), np.uint8)
+    full[:, row0:] = frames
+    o_lx, o_ly, o_in = orc.gather_soa(full, cams)
+    assert np.array_equal(inten, o_in[row0:])
+    assert ulp_diff(lx, o_lx[row0:]).max() <= LIGHT_ULP
+    assert ulp_diff(ly, o_ly[row0:]).max() <= LIGHT_ULP
+
+
+# ----------------------------------------------------------------------------- PTM fit
+def test_ptm_fit_frames_vs_oracle_and_reference(torch_cuda, ref_small):
+    coef, bad = gpu_fit_frames(torch_cuda, ref_small["frames"], ref_small["cams"])
+    assert bad == 0
+    n, rows, cols = ref_small["frames"].shape
+    c = coef.cpu().numpy().T                                           # (P, 6)
+    ref = orc.ptm_fit_batch(ref_small["lx"], ref_small["ly"], ref_small["inten"]).reshape(-1, 6)
+    assert coef_rel_err(c, ref) < PTM_COEF_RTOL
+    # against the unmodified reference's grids (its libm powf rounding included): 1e-4 budget
+    ax = orc.light_axis()
+    for k, (y, x) in enumerate(ref_small["keep"]):
+        g = orc.ptm_grid(c[y * cols + x], ax)
+        r = ref_small["ptm_grids"][k]
+        assert np.max(np.abs(g - r)) <= 1e-6 * np.max(np.abs(r))
+
+
+@pytest.mark.parametrize("rows,cols,n,row0", [(4, 4, 6, 0), (7, 19, 37, 3), (12, 50, 515, 0), (3, 130, 64, 9)])
+def test_ptm_fit_frames_shapes(torch_cuda, rows, cols, n, row0):
+    from rti_b200 import synthetic
+    frames, cams = synthetic.lambertian_stack(rows, cols, n, seed=n, row0=row0, rows_total=rows + row0)
+    coef, bad = gpu_fit_frames(torch_cuda, frames, cams, row0=row0)
+    assert bad == 0
+    full = np.zeros((n, rows + row0, cols), np.uint8)
+    full[:, row0:] = frames
+    lx, ly, inten = orc.gather_soa(full, cams)
+    ref = orc.ptm_fit_batch(lx[row0:], ly[row0:], inten[row0:]).reshape(-1, 6)
+    tol = 1e-7 if n == 6 else PTM_COEF_RTOL                            # N = 6 is exactly determined
+    assert coef_rel_err(coef.cpu().numpy().T, ref) < tol
+
+
+def test_ptm_fit_soa_matches_frames_path(torch_cuda):
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    rows, cols, n = 6, 21, 203
+    frames, cams = synthetic.lambertian_stack(rows, cols, n, seed=8)
+    lx, ly, inten = orc.gather_soa(frames, cams)
+    p = rows * cols
+    coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_soa", dev(torch, lx).data_ptr(), dev(torch, ly).data_ptr(),
+               dev(torch, inten).data_ptr(), p, n, coef.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0
+    ref = orc.ptm_fit_batch(lx, ly, inten).reshape(-1, 6)
+    assert coef_rel_err(coef.cpu().numpy().T, ref) < PTM_COEF_RTOL
+    fused, _ = gpu_fit_frames(torch, frames, cams)
+    assert coef_rel_err(coef.cpu().numpy().T, fused.cpu().numpy().T) < 1e-11
+
+
+def test_ptm_analytic_kat(torch_cuda):
+    """Intensities from a known biquadratic of the per-pixel light vectors are recovered."""
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    rng = np.random.default_rng(0)
+    n, p = 90, 64
+    lx = rng.uniform(-0.9, 0.9, (p, n)).astype(np.float32)
+    ly = rng.uniform(-0.9, 0.9, (p, n)).astype(np.float32)
+    true = np.array([-40.0, 25.0, 10.0, 3.0, -7.0, 120.0])
+    vals = np.rint(orc.ptm_design(lx, ly) @ true).astype(np.int32)     # integer intensities
+    coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+    _capi.call("rti_ptm_fit_soa", dev(torch, lx).data_ptr(), dev(torch, ly).data_ptr(),
+               dev(torch, vals).data_ptr(), p, n, coef.data_ptr(), p, None, None)
+    torch.cuda.synchronize()
+    ref = orc.ptm_fit_batch(lx, ly, vals)
+    assert coef_rel_err(coef.cpu().numpy().T, ref) < PTM_COEF_RTOL
+    assert np.max(np.abs(coef.cpu().numpy().T - true)) < 1.0            # rounding noise only
+
+
+def test_ptm_singular_pixels_are_flagged(torch_cuda):
+    """All light samples identical -> rank-1 design matrix: flagged, coefficients NaN."""
+    from rti_b200 import _capi
+    torch = torch_cuda
+    n, p = 12, 3
+    lx = np.full((p, n), 0.25, np.float32)
+    ly = np.full((p, n), -0.5, np.float32)
+    lx[1] = np.linspace(-0.8, 0.8, n)
+    ly[1] = np.linspace(0.7, -0.6, n) ** 2                                # pixel 1 is fine
+    vals = np.arange(p * n, dtype=np.int32).reshape(p, n)
+    coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_soa", dev(torch, lx).data_ptr(), dev(torch, ly).data_ptr(),
+               dev(torch, vals).data_ptr(), p, n, coef.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 2
+    c = coef.cpu().numpy()
+    assert np.all(np.isnan(c[:, 0])) and np.all(np.isnan(c[:, 2])) and np.all(np.isfinite(c[:, 1]))
+
+
+def test_ptm_shared_light_path(torch_cuda):
+    """Same light vector for every pixel: coef = pinv(design) . I, one contraction."""
+    from rti_b200 import _capi
+    torch = torch_cuda
+    rng = np.random.default_rng(4)
+    n, rows, cols = 77, 5, 23
+    lu = rng.uniform(-0.9, 0.9, n).astype(np.float32)
+    lv = rng.uniform(-0.9, 0.9, n).astype(np.float32)
+    frames = rng.integers(0, 256, (n, rows, cols), dtype=np.uint8)
+    design = orc.ptm_design(lu, lv)
+    u, s, vt = np.linalg.svd(design, full_matrices=False)
+    pinv = (vt.T / s) @ u.T                                            # (6, n), the reference's SVD solve
+    p = rows * cols
+    coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+    _capi.call("rti_ptm_fit_shared", dev(torch, frames).data_ptr(), p, dev(torch, pinv).data_ptr(), n, p,
+               coef.data_ptr(), p, None)
+    torch.cuda.synchronize()
+    lx = np.broadcast_to(lu, (rows, cols, n))
+    ly = np.broadcast_to(lv, (rows, cols, n))
+    inten = np.transpose(frames, (1, 2, 0)).astype(np.int32)
+    ref = orc.ptm_fit_batch(lx, ly, inten).reshape(-1, 6)
+    assert coef_rel_err(coef.cpu().numpy().T, ref) < PTM_COEF_RTOL
+
+
+# ---------------------------------------------------------------------- grid evaluation
+def _random_coef(p, seed=0):
+    rng = np.random.default_rng(seed)
+    return rng.normal(0, 60, (6, p)) + np.array([0, 0, 0, 0, 0, 120.0])[:, None]
+
+
+@pytest.mark.parametrize("p,g_step", [(36, 0.02), (1, 0.02), (1027, 0.1), (4096, 0.25), (255, 0.02)])
+def test_ptm_table_vs_oracle(torch_cuda, p, g_step):
+    from rti_b200 import _capi
+    torch = torch_cuda
+    coef = _random_coef(p, seed=p)
+    ax = orc.light_axis(g_step)
+    g = ax.size
+    table = torch.empty((g, g, p), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_table", dev(torch, coef).data_ptr(), p, p, dev(torch, ax).data_ptr(), g,
+               table.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert int(bad.item()) == 0
+    grids = orc.ptm_grid(coef.T, ax)                                    # (p, g, g)
+    ref = orc.table_from_grids(grids.reshape(p, 1, g, g))[:, :, :, 0]   # (g, g, p)
+    got = table.cpu().numpy()
+    diff = got != ref
+    # the regrouped fp64 evaluation may flip the truncation only on an integer boundary
+    gt = np.transpose(grids, (1, 2, 0))
+    assert np.all(np.abs(gt[diff] - np.rint(gt[diff])) < 1e-9)
+    assert np.count_nonzero(diff) <= 1e-6 * diff.size + 1
+    assert np.all(np.abs(got[diff] - ref[diff]) <= 1) if diff.any() else True
+
+
+def test_ptm_table_reference_golden(torch_cuda, ref_small):
+    """frames -> fused fit -> table equals the unmodified reference's prepare_images_data."""
+    from rti_b200 import _capi
+    torch = torch_cuda
+    coef, _ = gpu_fit_frames(torch, ref_small["frames"], ref_small["cams"])
+    ax = orc.light_axis()
+    p = coef.shape[1]
+    table = torch.empty((100, 100, p), dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_table", coef.data_ptr(), p, p, dev(torch, ax).data_ptr(), 100, table.data_ptr(), p,
+               None, None)
+    torch.cuda.synchronize()
+    ref = ref_small["table_ptm"].reshape(100, 100, p)
+    diff = table.cpu().numpy() != ref
+    assert np.count_nonzero(diff) == 0
+
+
+def test_ptm_table_flags_unrepresentable(torch_cuda):
+    from rti_b200 import _capi
+    torch = torch_cuda
+    coef = _random_coef(8)
+    coef[5, 3] = np.nan
+    coef[0, 6] = 5e9
+    ax = orc.light_axis()
+    table = torch.empty((100, 100, 8), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_table", dev(torch, coef).data_ptr(), 8, 8, dev(torch, ax).data_ptr(), 100,
+               table.data_ptr(), 8, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert int(bad.item()) >= 1
+
+
+def test_ptm_grids_vs_oracle(torch_cuda):
+    from rti_b200 import _capi
+    torch = torch_cuda
+    p = 19
+    coef = _random_coef(p, seed=3)
+    ax = orc.light_axis()
+    grids = torch.empty((p, 100, 100), dtype=torch.float64, device="cuda")
+    _capi.call("rti_ptm_grids", dev(torch, coef).data_ptr(), p, p, dev(torch, ax).data_ptr(), 100,
+               grids.data_ptr(), None)
+    torch.cuda.synchronize()
+    ref = orc.ptm_grid(coef.T, ax)
+    assert np.max(np.abs(grids.cpu().numpy() - ref)) <= 1e-12 * np.max(np.abs(ref))
+
+
+def test_grids_to_table_transposes_and_truncates(torch_cuda):
+    from rti_b200 import _capi
+    torch = torch_cuda
+    rng = np.random.default_rng(1)
+    p, g = 45, 10
+    grids = rng.normal(0, 300, (p, g, g))
+    grids[0, 0, 0] = -172.91
+    table = torch.empty((g, g, p), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_grids_to_table", dev(torch, grids).data_ptr(), p, g, table.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    ref = orc.table_from_grids(grids.reshape(p, 1, g, g))[:, :, :, 0]
+    assert np.array_equal(table.cpu().numpy(), ref) and table[0, 0, 0].item() == -172
+    assert int(bad.item()) == 0
+    grids[3, 2, 1] = np.inf
+    _capi.call("rti_grids_to_table", dev(torch, grids).data_ptr(), p, g, table.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert int(bad.item()) >= 1
+
+
+# --------------------------------------------------------------------------- relighting
+def test_relight_reproduces_table_at_grid_nodes(torch_cuda, relight_golden):
+    from rti_b200 import _capi, relighting
+    torch = torch_cuda
+    rows = cols = 64
+    p = rows * cols
+    coef = _random_coef(p, seed=11)
+    ax = orc.light_axis()
+    d_coef = dev(torch, coef)
+    table = torch.empty((100, 100, p), dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_table", d_coef.data_ptr(), p, p, dev(torch, ax).data_ptr(), 100, table.data_ptr(), p,
+               None, None)
+    hsv = relight_golden["hsv"]                                          # (64, 64, 3)
+    rl = relighting.Relighter(d_coef, rows, cols, hsv_roi=hsv)
+    rl_v = relighting.Relighter(d_coef, rows, cols)
+    tab = table.cpu().numpy().reshape(100, 100, rows, cols)
+    for (x, y) in [(0, 0), (200, 200), (399, 13), (123, 321), (400, 400)]:
+        lx, ly = orc.cursor_to_light(x, y, 400, 400)
+        ref_bgr = orc.relight_from_table(tab, hsv, lx, ly)
+        got = rl.render_cursor(x, y, shape=(400, 400)).cpu().numpy()
+        assert np.array_equal(got, ref_bgr)
+        v = rl_v.render_cursor(x, y, shape=(400, 400)).cpu().numpy()
+        assert np.array_equal(v, orc.clamp_values(tab[orc.light_to_index(ly)][orc.light_to_index(lx)]))
+        assert np.array_equal(relighting.relight_from_table(
+            tab[orc.light_to_index(ly)][orc.light_to_index(lx)], hsv), ref_bgr)
+
+
+def test_relight_f32_map_within_one(torch_cuda):
+    from rti_b200 import relighting
+    torch = torch_cuda
+    rows = cols = 50
+    coef = _random_coef(rows * cols, seed=2)
+    exact = relighting.Relighter(dev(torch, coef), rows, cols).render(0.37, -0.81).cpu().numpy().astype(int)
+    fast = relighting.Relighter(dev(torch, coef), rows, cols, precision="f32").render(0.37, -0.81).cpu().numpy()
+    d = np.abs(exact - fast.astype(int))
+    assert d.max() <= 1 and np.count_nonzero(d) <= 0.01 * d.size
+
+
+def test_hsv2bgr_device_matches_cv2_golden(torch_cuda, relight_golden):
+    """Every V value through the device HSV->BGR against the committed cv2 output."""
+    from rti_b200 import relighting
+    hsv = relight_golden["hsv"]
+    out = relighting.relight_from_table(hsv[:, :, 2].astype(np.int32), hsv)
+    assert np.array_equal(out, relight_golden["bgr"])
+
+
+# ---------------------------------------------------------------- call surface, end to end
+def test_call_surface_matches_reference_outputs(torch_cuda, ref_small, monkeypatch, tmp_path):
+    import rti_b200
+    from rti_b200 import synthetic
+    frames, cams = ref_small["frames"], ref_small["cams"]
+    monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", frames.shape[1])
+    data = rti_b200.compute_intensities(synthetic.as_records(frames, cams))
+    assert len(data) == 3 and data[0].shape == ref_small["lx"].shape
+    assert np.array_equal(np.asarray(data[2]), ref_small["inten"])
+    assert np.array_equal(data[2][1][2], ref_small["inten"][1][2])       # [y][x] -> (N,)
+    assert ulp_diff(np.asarray(data[0]), ref_small["lx"]).max() <= LIGHT_ULP
+    res = rti_b200.interpolate_intensities(data, interpolate_PTM=True)
+    assert len(res) == frames.shape[1]
+    for k, (y, x) in enumerate(ref_small["keep"]):
+        g = res[y][x]
+        assert g.shape == (100, 100) and g.dtype == np.float64
+        r = ref_small["ptm_grids"][k]
+        assert np.max(np.abs(g - r)) <= 1e-6 * np.max(np.abs(r))
+    images = rti_b200.prepare_images_data(res)
+    assert len(images) == 100 and len(images[0]) == 100
+    assert images[3][7].dtype == np.int32 and images[3][7].flags.writeable
+    assert np.array_equal(np.array(images), ref_small["table_ptm"])
+    # plain ndarray inputs (what the reference's own compute_intensities returns) take the SoA kernel
+    res2 = rti_b200.interpolate_intensities((ref_small["lx"], ref_small["ly"], ref_small["inten"]),
+                                            interpolate_PTM=True)
+    assert np.array_equal(np.array(rti_b200.prepare_images_data(res2)), ref_small["table_ptm"])
+    # nested-list input to prepare_images_data (the reference's interpolate output type)
+    nested = res.to_list()
+    assert np.array_equal(np.array(rti_b200.prepare_images_data(nested)), ref_small["table_ptm"])
+    # first_only = pixel (0, 0)
+    d1 = rti_b200.compute_intensities(synthetic.as_records(frames, cams), first_only=True)
+    r1 = rti_b200.interpolate_intensities(d1, interpolate_PTM=True, first_only=True)
+    i1 = rti_b200.prepare_images_data(r1, first_only=True)
+    assert i1[5][6].shape == (1, 1) and i1[5][6][0, 0] == ref_small["table_ptm"][5, 6, 0, 0]
+
+
+def test_compute_from_storage_writes_reference_pickle(torch_cuda, ref_small, monkeypatch, tmp_path):
+    import pickle
+    import rti_b200
+    from rti_b200 import synthetic
+    frames, cams = ref_small["frames"], ref_small["cams"]
+    monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", frames.shape[1])
+    monkeypatch.chdir(tmp_path)
+    (tmp_path / "assets").mkdir()
+    rti_b200.write_on_file(synthetic.as_records(frames, cams), "assets/frames_results_synth")
+    rti_b200.compute(video_name="synth", from_storage=True, interpolate_PTM=True)
+    with open("assets/interpolation_results_synth.pickle", "rb") as f:
+        table = pickle.load(f)
+    assert isinstance(table, list) and isinstance(table[0], list) and table[0][0].dtype == np.int32
+    assert np.array_equal(np.array(table), ref_small["table_ptm"])
+    values = table[40][60]
+    values[values > 255] = 255                                             # the relighter's in-place clamp
+    values[values <= 0] = 0
+
+
+def test_host_pipeline_tiles_match_single_shot(torch_cuda):
+    """rti_ptm_compute_host with many small row tiles == device path on the whole slab."""
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    rows_total, cols, n, row0, rows = 23, 36, 61, 5, 14
+    frames, cams = synthetic.lambertian_stack(rows_total, cols, n, seed=21)
+    ax = orc.light_axis(0.1)
+    g = ax.size
+    p = rows * cols
+    h_table = torch.empty((g, g, p), dtype=torch.int32).pin_memory()
+    h_coef = torch.empty((6, p), dtype=torch.float64).pin_memory()
+    h_frames = torch.from_numpy(frames).pin_memory()
+    for tile_rows in (3, 0):
+        h_table.fill_(-1)
+        _capi.call("rti_ptm_compute_host", h_frames.data_ptr(), cams.ctypes.data, n, rows_total, cols, row0, rows,
+                   ax.ctypes.data, g, h_table.data_ptr(), h_coef.data_ptr(), tile_rows)
+        lx, ly, inten = orc.gather_soa(frames, cams)
+        ref = orc.ptm_fit_batch(lx[row0:row0 + rows], ly[row0:row0 + rows], inten[row0:row0 + rows]).reshape(-1, 6)
+        assert coef_rel_err(h_coef.numpy().T, ref) < PTM_COEF_RTOL
+        ref_tab = orc.table_from_grids(orc.ptm_grid(ref, ax).reshape(p, 1, g, g))[:, :, :, 0]
+        assert np.count_nonzero(h_table.numpy() != ref_tab) == 0
+    _capi.call("rti_destroy")
+
+
+# ------------------------------------------------------- properties at BASELINE sizes
+def test_full_size_properties(torch_cuda):
+    """Config 3 geometry on a 1024-column slab with N=500: size-independent properties.
+    (a) row-slab independence: fitting rows [r0, r1) alone equals the same rows of a larger fit;
+    (b) linearity of the fit in the intensities: coef(I1 + I2) = coef(I1) + coef(I2);
+    (c) the table image of the grid node (lu, lv) equals the relit frame for that direction."""
+    from rti_b200 import _capi, relighting, synthetic
+    torch = torch_cuda
+    rows, cols, n = 64, 1024, 500
+    rng = np.random.default_rng(0)
+    cams = synthetic.camera_positions(1024, cols, n, rng)
+    f1 = rng.integers(0, 128, (n, rows, cols), dtype=np.uint8)
+    f2 = rng.integers(0, 128, (n, rows, cols), dtype=np.uint8)
+    c1, b1 = gpu_fit_frames(torch, f1, cams, row0=200)
+    c2, _ = gpu_fit_frames(torch, f2, cams, row0=200)
+    c12, _ = gpu_fit_frames(torch, f1 + f2, cams, row0=200)
+    assert b1 == 0
+    scale = c12.abs().max().item()
+    assert (c1 + c2 - c12).abs().max().item() < 1e-10 * scale            # (b)
+    sub, _ = gpu_fit_frames(torch, f1[:, 16:32], cams, row0=216)
+    assert torch.equal(sub, c1.view(6, rows, cols)[:, 16:32].reshape(6, -1))   # (a) bit-identical
+    # sampled oracle check at full N
+    lx, ly, inten = orc.gather_soa(np.concatenate([np.zeros((n, 200, 8), np.uint8), f1[:, :, :8]], axis=1), cams)
+    ref = orc.ptm_fit_batch(lx[200:203], ly[200:203], inten[200:203]).reshape(-1, 6)
+    got = c1.view(6, rows, cols)[:, :3, :8].reshape(6, -1).cpu().numpy().T
+    assert coef_rel_err(got, ref) < PTM_COEF_RTOL
+    ax = orc.light_axis()
+    p = rows * cols
+    table = torch.empty((100, 100, p), dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_table", c1.data_ptr(), p, p, dev(torch, ax).data_ptr(), 100, table.data_ptr(), p, None, None)
+    rl = relighting.Relighter(c1, rows, cols)
+    for v, u in [(0, 0), (99, 99), (50, 17), (3, 88)]:
+        frame = rl.render(ax[u], ax[v])
+        assert torch.equal(frame.view(-1).to(torch.int32), table[v, u].clamp(0, 255))   # (c)

@@ -1,0 +1,111 @@
+"""Host-side logic that needs no GPU: the call surface's argument checks and messages,
+the grid, the relighting index arithmetic, file formats, row partitioning, synthetic data."""
+import os
+import pickle
+
+import numpy as np
+import pytest
+
+import rti_b200
+from rti_b200 import analysis, relighting, sharding, synthetic
+import rti_oracle as orc
+
+
+def test_light_axis_matches_oracle_and_follows_constants(monkeypatch):
+    assert np.array_equal(analysis.light_axis(), orc.light_axis())
+    monkeypatch.setattr(rti_b200.constants, "INTERPOLATION_PARAM", 0.05)
+    assert analysis.light_axis().size == 40
+
+
+def test_reference_error_messages():
+    # same bare Exceptions and texts as analysis.py:205-206, 332-333, 384-385
+    for bad in (None, []):
+        with pytest.raises(Exception, match="Error computing intensities: results are empty"):
+            rti_b200.compute_intensities(bad)
+        with pytest.raises(Exception, match="Error preparing images: results are empty"):
+            rti_b200.prepare_images_data(bad)
+    for bad in (None, (1, 2)):
+        with pytest.raises(Exception, match="Error computing interpolation: results are empty or invalid"):
+            rti_b200.interpolate_intensities(bad)
+    with pytest.raises(Exception, match="Storage file not found!"):
+        rti_b200.read_from_file("/nonexistent/frames_results_x")
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    frames, cams = synthetic.random_stack(4, 4, 8)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        rti_b200.compute_intensities(synthetic.as_records(frames, cams), first_only=True)
+
+
+def test_file_round_trip_uses_reference_layout(tmp_path):
+    frames, cams = synthetic.random_stack(5, 5, 3)
+    recs = synthetic.as_records(frames, cams)
+    base = str(tmp_path / "frames_results_synth")
+    rti_b200.write_on_file(recs, base)                       # compressed -> .pbz2 (utilities.py:61-64)
+    assert os.path.isfile(base + ".pbz2")
+    import bz2
+    with bz2.BZ2File(base + ".pbz2", "rb") as f:             # what the reference's reader does
+        back = pickle.load(f)
+    assert len(back) == 3 and back[0][0].dtype == np.uint8 and back[0][1].shape == (3,)
+    back2 = rti_b200.read_from_file(base)
+    assert np.array_equal(back2[2][0], frames[2])
+    table = [[np.zeros((2, 2), np.int32) for _ in range(3)] for _ in range(3)]
+    rti_b200.write_on_file(table, base + "_t", compressed=False)
+    with open(base + "_t.pickle", "rb") as f:
+        t = pickle.load(f)
+    t[1][2][t[1][2] <= 0] = 0                                # consumer mutates in place (interactive_relighting.py:35-36)
+    assert t[1][2].flags.writeable
+
+
+def test_cursor_and_index_arithmetic(relight_golden):
+    g = relight_golden
+    for x, l, idx in zip(g["cursor"], g["light"], g["index"]):
+        lx, ly = relighting.cursor_to_light(int(x), int(x), (400, 400))
+        assert lx == l == ly
+        assert relighting.light_to_index(lx) == idx
+
+
+def test_row_partition():
+    assert sharding.row_partition(4096, 8) == [(i * 512, 512) for i in range(8)]
+    parts = sharding.row_partition(10, 4)
+    assert parts == [(0, 2), (2, 2), (4, 3), (7, 3)]          # remainder on the last ranks
+    assert sum(n for _, n in parts) == 10
+    assert sharding.row_partition(2, 4) == [(0, 0), (0, 0), (0, 1), (1, 1)]
+    assert sharding.row_partition(0, 2) == [(0, 0), (0, 0)]
+    with pytest.raises(ValueError):
+        sharding.row_partition(4, 0)
+
+
+def test_synthetic_is_seeded_and_slab_consistent():
+    f1, c1 = synthetic.lambertian_stack(8, 8, 5, seed=2)
+    f2, c2 = synthetic.lambertian_stack(8, 8, 5, seed=2)
+    assert np.array_equal(f1, f2) and np.array_equal(c1, c2)
+    assert f1.dtype == np.uint8 and c1.dtype == np.float64 and c1.shape == (5, 3)
+    # a slab sees the same cameras as the full ROI
+    _, c3 = synthetic.lambertian_stack(4, 8, 5, seed=2, row0=4, rows_total=8)
+    assert np.array_equal(c1, c3)
+    recs = synthetic.as_records(f1, c1)
+    assert len(recs) == 5 and recs[0][0].shape == (8, 8)
+
+
+def test_stack_frames_validates_roi_size():
+    recs = [(np.zeros((3, 3), np.uint8), np.zeros(3))]
+    with pytest.raises(IndexError):
+        analysis._stack_frames(recs, 4, 4)
+
+
+def test_install_rebinds_reference_module():
+    import types
+    fake = types.ModuleType("analysis")
+    fake.cst = types.SimpleNamespace(ROI_DIAMETER=7, INTERPOLATION_PARAM=0.5)
+    old = analysis._cst
+    try:
+        rti_b200.install(fake)
+        assert fake.compute_intensities is rti_b200.compute_intensities
+        assert fake.prepare_images_data is rti_b200.prepare_images_data
+        assert analysis.light_axis().size == 4               # now reads the reference's constants
+    finally:
+        analysis._cst = old
