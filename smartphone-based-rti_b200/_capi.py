@@ -109,4 +109,6 @@ def check(status: int, what: str = "") -> None:
 
 
 def call(name: str, *args) -> None:
+    # numpy integers (e.g. an index taken from an array) are not accepted by ctypes
+    args = [int(a) if hasattr(a, "__index__") and not isinstance(a, (int, bool)) else a for a in args]
     check(getattr(load(), name)(*args), name)

@@ -1,20 +1,458 @@
-// Linear RBF path (placeholder until the batched Cholesky kernels land).
+// Linear radial-basis-function path (reference: _interpolate_RBF, analysis.py:249-260,
+// i.e. scipy.interpolate.Rbf(lx, ly, values, function='linear') evaluated on the grid).
+//
+// Fit.  scipy solves A w = d with A[j][k] = |n_j - n_k| (symmetric, zero diagonal,
+// indefinite -> pivoted solver).  phi(r) = r is conditionally negative definite, so
+// eliminating node 0 gives the (n-1) x (n-1) matrix
+//     B[j][k] = a_j + a_k - |n_j - n_k|,   a_j = |n_j - n_0|          (j, k = 1..n-1)
+// which is symmetric POSITIVE definite for distinct nodes: Cholesky, no pivoting.
+// With B p = d_0*1 - d', B q = a, sigma = (d_0 - a.p)/(a.q):
+//     w' = p + sigma*q,   w_0 = sigma - sum(w')
+// is exactly the solution of A w = d.  Everything is fp64.
+//
+// One CTA factorises one pixel's matrix with a left-looking blocked Cholesky on 64 x 64
+// tiles.  B is generated on the fly from the node coordinates (never stored); L lives in
+// an L2-resident workspace in 16 KB blocks laid out [k][row] so that every operand chunk
+// is one contiguous cp.async stream into shared memory.  The two right-hand sides ride
+// along as two extra rows of the matrix, which performs the forward substitution inside
+// the factorisation; only the backward substitution remains.
 #include "common.cuh"
+
+namespace rti {
+
+constexpr int TS = 64;                  // tile edge
+constexpr int KC = 32;                  // k-chunk depth of one staged operand block
+constexpr int BLK = KC * TS;            // doubles per block (16 KB)
+constexpr int RBF_THREADS = 256;
+constexpr int SD_LD = TS + 1;           // padded leading dimension of the potrf scratch
+
+__host__ __device__ inline int rbf_mpad(int n) { return ((n - 1 + 2 + TS - 1) / TS) * TS; }
+
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+// |d| for d2 >= 0 in fp64 (MUFU seed + Newton, ~2 ulp); 0 for d2 == 0
+__device__ __forceinline__ double sqrt_pos(double d2) { return d2 > 0.0 ? d2 * rsqrt_pos(d2) : 0.0; }
+
+// acc[i][j] -= sum_k A[k][r0+i] * B[k][c0+j] over one staged chunk of `depth` k-rows
+__device__ __forceinline__ void mma_chunk(double (&acc)[4][4], const double *__restrict__ sA,
+                                          const double *__restrict__ sB, int r0, int c0, int depth) {
+#pragma unroll 4
+    for (int k = 0; k < depth; ++k) {
+        const double2 a01 = *reinterpret_cast<const double2 *>(sA + k * TS + r0);
+        const double2 a23 = *reinterpret_cast<const double2 *>(sA + k * TS + r0 + 2);
+        const double2 b01 = *reinterpret_cast<const double2 *>(sB + k * TS + c0);
+        const double2 b23 = *reinterpret_cast<const double2 *>(sB + k * TS + c0 + 2);
+        const double a[4] = {a01.x, a01.y, a23.x, a23.y};
+        const double b[4] = {b01.x, b01.y, b23.x, b23.y};
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[i][j] = fma(-a[i], b[j], acc[i][j]);
+    }
+}
+
+__device__ __forceinline__ double block_sum(double v, double *s_red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < RBF_THREADS / 32; ++w) t += s_red[w];
+    return t;
+}
+
+// Shared memory map (doubles):  [0, 4096) sA (2 chunk buffers)   [4096, 8192) sB (2 chunk buffers)
+//   the potrf scratch sD[64][65], the transposed C tile and the substitution vectors alias sA/sB
+//   [8192, 12288) sW = D^-T of the current block column   then sRsq[64], s_red[8], nodes (4 * n)
+__global__ void __launch_bounds__(RBF_THREADS, 2)
+rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const int32_t *__restrict__ inten,
+               int64_t n_pixels, int n, double *__restrict__ weights, double *__restrict__ work,
+               int64_t work_stride, int32_t *__restrict__ bad) {
+    extern __shared__ __align__(16) double smem[];
+    double *sA = smem;
+    double *sB = smem + 2 * BLK;
+    double *sD = smem;                          // alias: [64][65]
+    double *sCk = smem;                         // alias: [64 k][64 r]
+    double *sW = smem + 4 * BLK;                // [64 k][64 c]: sW[k][c] = Dinv[c][k]
+    double *sRsq = sW + TS * TS;
+    double *s_red = sRsq + TS;
+    double *sx = s_red + 8;
+    double *sy = sx + n;
+    double *sa = sy + n;
+    double *sd = sa + n;
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int r0 = 16 * (warp >> 1) + 4 * (lane >> 3);          // micro-tile origin inside a 64x64 tile
+    const int c0 = 32 * (warp & 1) + 4 * (lane & 7);
+    const int M = n - 1;
+    const int mpad = rbf_mpad(n);
+    const int nT = mpad / TS, nKC = mpad / KC;
+    double *L = work + (int64_t)blockIdx.x * work_stride;       // blocks (it, kc) at (it*nKC + kc)*BLK
+    double *Wg = L + (int64_t)nT * nKC * BLK;                   // nT tiles of 64x64
+
+    for (int64_t pix = blockIdx.x; pix < n_pixels; pix += gridDim.x) {
+        __syncthreads();
+        for (int i = t; i < n; i += RBF_THREADS) {
+            sx[i] = (double)lx[pix * n + i];
+            sy[i] = (double)ly[pix * n + i];
+            sd[i] = (double)inten[pix * n + i];
+        }
+        __syncthreads();
+        for (int i = t; i < n; i += RBF_THREADS) {
+            const double dx = sx[i] - sx[0], dy = sy[i] - sy[0];
+            sa[i] = sqrt_pos(fma(dx, dx, dy * dy));
+        }
+        __syncthreads();
+        bool ok = true;
+
+        for (int kb = 0; kb < nT; ++kb) {
+            for (int it = kb; it < nT; ++it) {
+                // ---- generate the tile of the bordered matrix in registers
+                double acc[4][4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int gr = it * TS + r0 + i;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const int gc = kb * TS + c0 + j;
+                        double v;
+                        if (gc >= M) v = (gr == gc) ? 1.0 : 0.0;                    // padding: identity
+                        else if (gr < M) {
+                            const double dx = sx[gr + 1] - sx[gc + 1], dy = sy[gr + 1] - sy[gc + 1];
+                            v = sa[gr + 1] + sa[gc + 1] - sqrt_pos(fma(dx, dx, dy * dy));
+                        } else if (gr == M) v = sd[0] - sd[gc + 1];                 // rhs 1: d0*1 - d'
+                        else if (gr == M + 1) v = sa[gc + 1];                       // rhs 2: a
+                        else v = 0.0;
+                        acc[i][j] = v;
+                    }
+                }
+                // ---- acc -= L[it][0:k0] . L[kb][0:k0]^T, operand chunks streamed with cp.async
+                const int nk = 2 * kb;
+                const bool diag = (it == kb);
+                auto issue = [&](int buf, int kc) {
+                    const double *ga = L + ((int64_t)it * nKC + kc) * BLK;
+                    const double *gb = L + ((int64_t)kb * nKC + kc) * BLK;
+#pragma unroll
+                    for (int i = 0; i < BLK * 8 / 16 / RBF_THREADS; ++i) {
+                        const int e = (t + i * RBF_THREADS) * 2;
+                        cp_async16(sA + buf * BLK + e, ga + e);
+                        if (!diag) cp_async16(sB + buf * BLK + e, gb + e);
+                    }
+                    cp_async_commit();
+                };
+                __syncthreads();                 // smem aliases of the previous tile are dead; L stores visible
+                if (nk > 0) issue(0, 0);
+                for (int kc = 0; kc < nk; ++kc) {
+                    if (kc + 1 < nk) { issue((kc + 1) & 1, kc + 1); cp_async_wait<1>(); }
+                    else cp_async_wait<0>();
+                    __syncthreads();
+                    const double *pa = sA + (kc & 1) * BLK;
+                    mma_chunk(acc, pa, diag ? pa : sB + (kc & 1) * BLK, r0, c0, KC);
+                    __syncthreads();
+                }
+
+                if (diag) {
+                    // ---- potrf of the 64x64 diagonal tile in shared memory
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int gr = kb * TS + r0 + i, gc = kb * TS + c0 + j;
+                            sD[(r0 + i) * SD_LD + c0 + j] = (gc >= M) ? ((gr == gc) ? 1.0 : 0.0) : acc[i][j];
+                        }
+                    const int ur = t >> 2;                       // this thread updates row ur, columns uc0 + 4m
+                    const int uc0 = t & 3;
+                    for (int j = 0; j < TS; ++j) {
+                        __syncthreads();
+                        const double piv = sD[j * SD_LD + j];
+                        const int gj = kb * TS + j;
+                        // relative pivot test against the original diagonal 2*a_j (duplicate nodes -> 0)
+                        const double ref = (gj < M) ? 2.0 * sa[gj + 1] : 1.0;
+                        if (!(piv > 1e-13 * ref) || !(piv > 0.0)) ok = false;
+                        const double rs = rsqrt(piv);
+                        if (t == 0) sRsq[j] = rs;
+                        const double ip = rs * rs;
+                        if (ur > j) {
+                            const double lrj = sD[ur * SD_LD + j] * ip;
+                            for (int c = uc0 + ((j + 1 - uc0 + 3) & ~3); c <= ur; c += 4)
+                                if (kb * TS + c < M)
+                                    sD[ur * SD_LD + c] = fma(-lrj, sD[c * SD_LD + j], sD[ur * SD_LD + c]);
+                        }
+                    }
+                    __syncthreads();
+                    // scale columns: L[r][c] = S[r][c]/sqrt(piv_c); zero the strict upper triangle
+                    for (int e = t; e < TS * TS; e += RBF_THREADS) {
+                        const int r = e >> 6, c = e & 63;
+                        const double v = sD[r * SD_LD + c];
+                        sD[r * SD_LD + c] = (c < r) ? v * sRsq[c] : ((c == r) ? v * sRsq[c] : 0.0);
+                    }
+                    __syncthreads();
+                    // ---- Dinv by forward substitution, 4 threads per column k: sW[k][c] = Dinv[c][k]
+                    {
+                        const int k = t >> 2, q = t & 3;
+                        for (int c = 0; c < TS; ++c) {
+                            double part = 0.0;
+                            for (int p = k + q; p < c; p += 4) part = fma(sD[c * SD_LD + p], sW[k * TS + p], part);
+                            part += __shfl_xor_sync(0xffffffffu, part, 1);
+                            part += __shfl_xor_sync(0xffffffffu, part, 2);
+                            double v;
+                            if (c < k) v = 0.0;
+                            else if (c == k) v = sRsq[c];                            // 1/D[k][k]
+                            else v = -part * sRsq[c];                               // 1/D[c][c] = rsqrt(piv_c)
+                            if (q == 0) sW[k * TS + c] = v;
+                            __syncwarp();
+                        }
+                    }
+                    __syncthreads();
+                    // ---- store D (block layout [k=c][r]) and D^-T
+                    double *gd = L + ((int64_t)kb * nKC + 2 * kb) * BLK;
+                    for (int e = t; e < TS * TS; e += RBF_THREADS) {
+                        const int c = e >> 6, r = e & 63;
+                        gd[c * TS + r] = sD[r * SD_LD + c];                          // chunks 2kb, 2kb+1 are adjacent
+                        Wg[(int64_t)kb * TS * TS + e] = sW[e];
+                    }
+                } else {
+                    // ---- X = C . D^-T through the same micro-kernel: A operand = C^T staged [k=c][r]
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int gc = kb * TS + c0 + j, gr = it * TS + r0 + i;
+                            sCk[(c0 + j) * TS + r0 + i] = (gc >= M) ? ((gr == gc) ? 1.0 : 0.0) : acc[i][j];
+                        }
+                    __syncthreads();
+                    double x[4][4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) x[i][j] = 0.0;
+                    mma_chunk(x, sCk, sW, r0, c0, TS);                               // x = -C.D^-T
+                    double *gx = L + ((int64_t)it * nKC + 2 * kb) * BLK;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        double *dst = gx + (c0 + j) * TS + r0;
+                        *reinterpret_cast<double2 *>(dst) = make_double2(-x[0][j], -x[1][j]);
+                        *reinterpret_cast<double2 *>(dst + 2) = make_double2(-x[2][j], -x[3][j]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- backward substitution L^T x = z for both right-hand sides (z = rows M, M+1 of L)
+        double *x1 = smem, *x2 = smem + mpad, *t1 = smem + 2 * mpad, *t2 = smem + 3 * mpad;   // alias sA/sB
+        auto Lat = [&](int r, int c) -> double {
+            return L[((int64_t)(r >> 6) * nKC + (c >> 5)) * BLK + (c & 31) * TS + (r & 63)];
+        };
+        for (int c = t; c < mpad; c += RBF_THREADS) {
+            t1[c] = (c < M) ? Lat(M, c) : 0.0;
+            t2[c] = (c < M) ? Lat(M + 1, c) : 0.0;
+            x1[c] = 0.0;
+            x2[c] = 0.0;
+        }
+        __syncthreads();
+        for (int kb = nT - 1; kb >= 0; --kb) {
+            if (kb * TS >= M) continue;                       // tile of padding only
+            // s[c] = sum_{r >= (kb+1)*64, r < M} L[r][c] x[r]; one warp per column, lanes stride rows
+            for (int cl = warp; cl < TS; cl += RBF_THREADS / 32) {
+                const int c = kb * TS + cl;
+                double s1 = 0.0, s2 = 0.0;
+                for (int r = (kb + 1) * TS + lane; r < M; r += 32) {
+                    const double l = Lat(r, c);
+                    s1 = fma(l, x1[r], s1);
+                    s2 = fma(l, x2[r], s2);
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+                    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+                }
+                if (lane == 0) { t1[c] -= s1; t2[c] -= s2; }
+            }
+            __syncthreads();
+            // x_kb[c] = sum_{k >= c} Dinv[k][c] * t[k]  (Dinv[k][c] = W[c][k], W stored [c][k] k-fastest)
+            if (t < 2 * TS) {
+                const int cl = t & 63;
+                const double *tv = (t < TS) ? t1 : t2;
+                const double *wrow = Wg + (int64_t)kb * TS * TS + cl * TS;
+                double s = 0.0;
+                for (int k = cl; k < TS; ++k) s = fma(wrow[k], tv[kb * TS + k], s);
+                ((t < TS) ? x1 : x2)[kb * TS + cl] = (kb * TS + cl < M) ? s : 0.0;
+            }
+            __syncthreads();
+        }
+        // ---- sigma and the weights
+        double ap = 0.0, aq = 0.0;
+        for (int j = t; j < M; j += RBF_THREADS) {
+            ap = fma(sa[j + 1], x1[j], ap);
+            aq = fma(sa[j + 1], x2[j], aq);
+        }
+        ap = block_sum(ap, s_red);
+        aq = block_sum(aq, s_red);
+        const double sigma = (sd[0] - ap) / aq;
+        double sw = 0.0;
+        for (int j = t; j < M; j += RBF_THREADS) {
+            const double w = fma(sigma, x2[j], x1[j]);
+            weights[pix * n + j + 1] = w;
+            sw += w;
+        }
+        sw = block_sum(sw, s_red);
+        if (t == 0) {
+            weights[pix * n] = sigma - sw;
+            if (!ok && bad != nullptr) atomicAdd(bad, 1);
+        }
+        // `ok` is per thread; combine so that any thread's failure is reported once
+        const int any_bad = __syncthreads_or(!ok);
+        if (t == 0 && any_bad && ok && bad != nullptr) atomicAdd(bad, 1);
+    }
+}
+
+// --------------------------------------------------------------------------------------
+// Grid evaluation: value(v, u) = sum_k |(axis[u], axis[v]) - n_k| * w_k  (Rbf.__call__).
+// A CTA owns PB consecutive pixels and a chunk of grid rows; a thread owns one direction
+// and accumulates all PB pixels, so that table stores are PB*4 contiguous bytes.  Node
+// data is staged in shared memory chunk by chunk and read as broadcasts.
+// Bound: fp64 pipe (~10 issue slots per pixel.direction.node).
+// --------------------------------------------------------------------------------------
+constexpr int EV_THREADS = 256;
+constexpr int EV_KCH = 128;             // nodes staged per chunk
+
+template <int PB, bool TABLE>
+__global__ void __launch_bounds__(EV_THREADS)
+rbf_eval_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const double *__restrict__ weights,
+                int64_t n_pixels, int n, const double *__restrict__ axis, int g, void *__restrict__ out,
+                int64_t image_stride, int32_t *__restrict__ bad) {
+    __shared__ double s_x[PB][EV_KCH], s_y[PB][EV_KCH], s_w[PB][EV_KCH];
+    const int64_t p0 = (int64_t)blockIdx.x * PB;
+    const int64_t gg = (int64_t)g * g;
+    const int64_t d = (int64_t)blockIdx.y * EV_THREADS + threadIdx.x;        // direction index v*g + u
+    const bool live = d < gg;
+    const int v = live ? (int)(d / g) : 0, u = live ? (int)(d - (int64_t)v * g) : 0;
+    const double gx = axis[u], gy = axis[v];
+    double acc[PB];
+#pragma unroll
+    for (int q = 0; q < PB; ++q) acc[q] = 0.0;
+    for (int k0 = 0; k0 < n; k0 += EV_KCH) {
+        const int kc = min(EV_KCH, n - k0);
+        __syncthreads();
+        for (int e = threadIdx.x; e < PB * kc; e += EV_THREADS) {
+            const int q = e / kc, k = e - q * kc;
+            const int64_t p = (p0 + q < n_pixels) ? p0 + q : n_pixels - 1;
+            s_x[q][k] = (double)lx[p * n + k0 + k];
+            s_y[q][k] = (double)ly[p * n + k0 + k];
+            s_w[q][k] = weights[p * n + k0 + k];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < PB; ++q) {
+            double a = acc[q];
+#pragma unroll 4
+            for (int k = 0; k < kc; ++k) {
+                const double dx = gx - s_x[q][k], dy = gy - s_y[q][k];
+                const double d2 = fma(dx, dx, dy * dy);
+                // one Newton step on the MUFU seed: relative error ~1e-13
+                // (the clamp keeps the seed finite when d2 == 0: then d2 * r == 0 exactly)
+                double r = (double)rsqrtf(fmaxf((float)d2, 1e-30f));
+                r = r * fma(-(0.5 * d2) * r, r, 1.5);
+                a = fma(d2 * r, s_w[q][k], a);
+            }
+            acc[q] = a;
+        }
+    }
+    if (!live) return;
+    bool any_bad = false;
+    if (TABLE) {
+        int32_t *dst = reinterpret_cast<int32_t *>(out) + d * image_stride + p0;
+#pragma unroll
+        for (int q = 0; q < PB; ++q) {
+            if (p0 + q < n_pixels) {
+                if (!(fabs(acc[q]) < 2147483648.0)) any_bad = true;
+                dst[q] = trunc_i32(acc[q]);
+            }
+        }
+    } else {
+        double *dst = reinterpret_cast<double *>(out);
+#pragma unroll
+        for (int q = 0; q < PB; ++q)
+            if (p0 + q < n_pixels) dst[(p0 + q) * gg + d] = acc[q];
+    }
+    if (any_bad && bad != nullptr) atomicAdd(bad, 1);
+}
+
+}  // namespace rti
+
 using namespace rti;
 
-extern "C" int64_t rti_rbf_workspace_bytes(int n, int batch) { (void)n; (void)batch; return 0; }
-extern "C" int rti_rbf_fit_soa(const float *, const float *, const int32_t *, int64_t, int, double *, void *,
-                               int64_t, int, int32_t *, rti_stream_t) {
-    set_error("rti_rbf_fit_soa: not built yet");
-    return RTI_ERR_ARG;
+static size_t rbf_fit_smem(int n) {
+    return (size_t)(4 * BLK + TS * TS + TS + 8 + 4 * n) * sizeof(double);
 }
-extern "C" int rti_rbf_table(const float *, const float *, const double *, int64_t, int, const double *, int,
-                             int32_t *, int64_t, int32_t *, rti_stream_t) {
-    set_error("rti_rbf_table: not built yet");
-    return RTI_ERR_ARG;
+
+extern "C" int64_t rti_rbf_workspace_bytes(int n, int batch) {
+    if (n < 2 || batch < 1) return 0;
+    const int64_t mpad = rbf_mpad(n);
+    const int64_t nT = mpad / TS, nKC = mpad / KC;
+    return (int64_t)batch * (nT * nKC * BLK + nT * TS * TS) * (int64_t)sizeof(double);
 }
-extern "C" int rti_rbf_grids(const float *, const float *, const double *, int64_t, int, const double *, int,
-                             double *, rti_stream_t) {
-    set_error("rti_rbf_grids: not built yet");
-    return RTI_ERR_ARG;
+
+extern "C" int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten, int64_t n_pixels,
+                               int n, double *d_weights, void *d_work, int64_t work_bytes, int batch,
+                               int32_t *d_bad, rti_stream_t stream) {
+    RTI_REQUIRE(d_lx && d_ly && d_inten && d_weights && d_work, "rti_rbf_fit_soa: NULL pointer");
+    RTI_REQUIRE(n_pixels > 0 && batch > 0, "rti_rbf_fit_soa: empty input");
+    RTI_REQUIRE(n >= 2, "rti_rbf_fit_soa: need >= 2 nodes, got %d", n);
+    RTI_REQUIRE(work_bytes >= rti_rbf_workspace_bytes(n, batch), "rti_rbf_fit_soa: workspace too small");
+    RTI_REQUIRE((reinterpret_cast<uintptr_t>(d_work) & 15) == 0, "rti_rbf_fit_soa: workspace not 16-byte aligned");
+    const size_t smem = rbf_fit_smem(n);
+    RTI_REQUIRE(smem <= 227 * 1024, "rti_rbf_fit_soa: n = %d needs %zu bytes of shared memory (> 227 KB)", n, smem);
+    RTI_CUDA(cudaFuncSetAttribute(rbf_fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t grid = n_pixels < batch ? n_pixels : batch;
+    const int64_t stride = rti_rbf_workspace_bytes(n, 1) / (int64_t)sizeof(double);
+    rbf_fit_kernel<<<(unsigned)grid, RBF_THREADS, smem, as_stream(stream)>>>(
+        d_lx, d_ly, d_inten, n_pixels, n, d_weights, reinterpret_cast<double *>(d_work), stride, d_bad);
+    RTI_LAUNCHED("rbf_fit_kernel");
+    return RTI_OK;
+}
+
+template <bool TABLE>
+static int rbf_eval_launch(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels, int n,
+                           const double *d_axis, int g, void *d_out, int64_t image_stride, int32_t *d_bad,
+                           rti_stream_t stream, const char *who) {
+    RTI_REQUIRE(d_lx && d_ly && d_weights && d_axis && d_out, "%s: NULL pointer", who);
+    RTI_REQUIRE(n_pixels > 0 && n > 0 && g > 0 && g <= 2048, "%s: bad sizes", who);
+    const int64_t gg = (int64_t)g * g;
+    const unsigned gy = (unsigned)((gg + EV_THREADS - 1) / EV_THREADS);
+    if (TABLE) {
+        RTI_REQUIRE(image_stride >= n_pixels, "%s: image_stride < pixels", who);
+        const int64_t bx = (n_pixels + 7) / 8;
+        RTI_REQUIRE(bx <= 0x7fffffffLL, "%s: too many pixels", who);
+        rbf_eval_kernel<8, true><<<dim3((unsigned)bx, gy), EV_THREADS, 0, as_stream(stream)>>>(
+            d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_out, image_stride, d_bad);
+    } else {
+        RTI_REQUIRE(n_pixels <= 0x7fffffffLL, "%s: too many pixels", who);
+        rbf_eval_kernel<1, false><<<dim3((unsigned)n_pixels, gy), EV_THREADS, 0, as_stream(stream)>>>(
+            d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_out, 0, d_bad);
+    }
+    RTI_LAUNCHED("rbf_eval_kernel");
+    return RTI_OK;
+}
+
+extern "C" int rti_rbf_table(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels, int n,
+                             const double *d_axis, int g, int32_t *d_table, int64_t image_stride, int32_t *d_bad,
+                             rti_stream_t stream) {
+    return rbf_eval_launch<true>(d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_table, image_stride, d_bad,
+                                 stream, "rti_rbf_table");
+}
+
+extern "C" int rti_rbf_grids(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels, int n,
+                             const double *d_axis, int g, double *d_grids, rti_stream_t stream) {
+    return rbf_eval_launch<false>(d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_grids, 0, nullptr, stream,
+                                  "rti_rbf_grids");
 }
