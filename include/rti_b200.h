@@ -107,6 +107,17 @@ int rti_ptm_table(const double *d_coef, int64_t plane_stride, int64_t n_pixels,
 int rti_ptm_grids(const double *d_coef, int64_t plane_stride, int64_t n_pixels,
                   const double *d_axis, int g, double *d_grids, rti_stream_t stream);
 
+/* Fused compute_intensities + PTM fit + table (analysis.py:466-472 for interpolate_PTM=True) in
+ * one kernel: every CTA fits 256 pixels and then writes their table entries, so the fp64-bound
+ * fit of one CTA overlaps the HBM-bound stores of its neighbours.  Arguments as
+ * rti_ptm_fit_frames + rti_ptm_table; d_coef may be NULL when only the table is wanted;
+ * d_bad (may be NULL) is int32[2]: [0] singular pixels, [1] pixels with unrepresentable values. */
+int rti_ptm_fit_table_frames(const uint8_t *d_frames, int64_t frame_stride, const double *d_cams,
+                             int n, int row0, int rows, int cols, const double *d_axis, int g,
+                             double *d_coef, int64_t plane_stride,
+                             int32_t *d_table, int64_t image_stride, int32_t *d_bad,
+                             rti_stream_t stream);
+
 /* prepare_images_data on arbitrary input (analysis.py:400-409): d_grids float64
  * [n_pixels][g][g] -> d_table int32 [g][g][image_stride], truncating toward zero;
  * d_bad counts tiles holding NaN/inf/out-of-int32 values (reference: ValueError /

@@ -54,6 +54,7 @@ SIGNATURES = {
     "rti_ptm_fit_shared": (_i, [_p, _l, _p, _i, _l, _p, _l, _p]),
     "rti_ptm_table": (_i, [_p, _l, _l, _p, _i, _p, _l, _p, _p]),
     "rti_ptm_grids": (_i, [_p, _l, _l, _p, _i, _p, _p]),
+    "rti_ptm_fit_table_frames": (_i, [_p, _l, _p, _i, _i, _i, _i, _p, _i, _p, _l, _p, _l, _p, _p]),
     "rti_grids_to_table": (_i, [_p, _l, _i, _p, _l, _p, _p]),
     "rti_rbf_workspace_bytes": (_l, [_i, _i]),
     "rti_rbf_fit_soa": (_i, [_p, _p, _p, _l, _i, _p, _p, _l, _i, _p, _p]),

@@ -38,18 +38,24 @@ static inline cudaStream_t as_stream(rti_stream_t s) { return reinterpret_cast<c
 
 // ---- device math --------------------------------------------------------------------
 
-// 1/sqrt(d2) in fp64 for finite d2 > 0: MUFU.RSQ seed (2^-22) + two Newton steps.
-// Relative error ~2 ulp(fp64); the light vector is rounded to float32 afterwards
-// (analysis.py:230-231), so this matches the reference's sqrt + divide except when the
-// fp64 value sits within ~1e-16 relative of a float32 rounding boundary.
+// 1/sqrt(d2) in fp64 for finite d2 > 0: MUFU.RSQ64H seed (rsqrt.approx.f64, relative error
+// 2^-22.9, no float conversions) + one third-order step r(1 + e/2 + 3e^2/8), e = 1 - d2 r^2.
+// Truncation error 5e^3/16 < 2^-70, i.e. the result carries only fp64 rounding (~2 ulp).  The
+// light vector is rounded to float32 afterwards (analysis.py:230-231), so this matches the
+// reference's sqrt + divide except when the fp64 value sits within ~1e-16 relative of a
+// float32 rounding boundary.
 __device__ __forceinline__ double rsqrt_pos(double d2) {
-    double r = (double)rsqrtf((float)d2);
-    const double h = 0.5 * d2;
-    double t = h * r;
-    r = r * fma(-t, r, 1.5);
-    t = h * r;
-    r = r * fma(-t, r, 1.5);
-    return r;
+    double r;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d2));
+    const double t = d2 * r;
+    const double e = fma(-t, r, 1.0);
+    const double q = fma(0.375, e, 0.5);
+    return fma(r * e, q, r);
+}
+
+// uint8 -> double without the conversion pipe: 2^52 + v has v in its low mantissa bits.
+__device__ __forceinline__ double u8_to_double(unsigned v) {
+    return __hiloint2double(0x43300000, (int)v) - 4503599627370496.0;
 }
 
 // Unit light vector of pixel (xd, yd, 0) for camera (cx, cy, cz), cz2 = cz*cz:

@@ -133,15 +133,15 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
         // ---- compute
         RTI_CUDA(cudaStreamWaitEvent(c.s_comp, c.ev_h2d[b], 0));
         if (t >= 2) RTI_CUDA(cudaStreamWaitEvent(c.s_comp, c.ev_d2h[b], 0));  // coef[b]/table[b] drained
-        rc = rti_ptm_fit_frames(c.d_frames[b], tile_pixels, c.d_cams, n, row0 + r, tr, cols, c.d_coef[b],
-                                tile_pixels, c.d_bad, c.s_comp);
+        if (h_table) {
+            rc = rti_ptm_fit_table_frames(c.d_frames[b], tile_pixels, c.d_cams, n, row0 + r, tr, cols, c.d_axis, g,
+                                          c.d_coef[b], tile_pixels, c.d_table[b], tile_pixels, c.d_bad, c.s_comp);
+        } else {
+            rc = rti_ptm_fit_frames(c.d_frames[b], tile_pixels, c.d_cams, n, row0 + r, tr, cols, c.d_coef[b],
+                                    tile_pixels, c.d_bad, c.s_comp);
+        }
         if (rc != RTI_OK) return rc;
         RTI_CUDA(cudaEventRecord(c.ev_fit[b], c.s_comp));
-        if (h_table) {
-            rc = rti_ptm_table(c.d_coef[b], tile_pixels, tp, c.d_axis, g, c.d_table[b], tile_pixels,
-                               c.d_bad + 1, c.s_comp);
-            if (rc != RTI_OK) return rc;
-        }
         RTI_CUDA(cudaEventRecord(c.ev_comp[b], c.s_comp));
         // ---- D2H
         RTI_CUDA(cudaStreamWaitEvent(c.s_d2h, c.ev_comp[b], 0));

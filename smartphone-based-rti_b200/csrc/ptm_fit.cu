@@ -50,14 +50,14 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
             for (int j = 0; j < FIT_UNROLL; ++j) {
                 float lu, lv;
                 light_vector(s_cam[i + j][0], s_cam[i + j][1], s_cam[i + j][2], xd, yd, lu, lv);
-                ne.add(lu, lv, (double)v[j]);
+                ne.add(lu, lv, u8_to_double(v[j]));
             }
         }
         for (; i < fc; ++i) {
             const uint8_t v = __ldg(src + (int64_t)(f0 + i) * frame_stride);
             float lu, lv;
             light_vector(s_cam[i][0], s_cam[i][1], s_cam[i][2], xd, yd, lu, lv);
-            ne.add(lu, lv, (double)v);
+            ne.add(lu, lv, u8_to_double(v));
         }
     }
     double a[6];

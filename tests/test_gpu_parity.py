@@ -581,3 +581,45 @@ def test_rbf_call_surface(torch_cuda, ref_small, monkeypatch):
     lx[0, 0, 5], ly[0, 0, 5] = lx[0, 0, 6], ly[0, 0, 6]
     with pytest.raises(rti_b200.RtiSingularError):
         rti_b200.interpolate_intensities((lx, ly, inten))
+
+
+# ------------------------------------------------------------------------- fused kernel
+@pytest.mark.parametrize("rows,cols,n,row0,g_step", [(6, 6, 40, 0, 0.02), (5, 103, 77, 2, 0.1), (3, 257, 31, 0, 0.25),
+                                                      (16, 64, 130, 7, 0.02)])
+def test_fused_kernel_equals_two_kernel_path(torch_cuda, rows, cols, n, row0, g_step):
+    """rti_ptm_fit_table_frames is bit-identical to rti_ptm_fit_frames + rti_ptm_table."""
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    frames, cams = synthetic.lambertian_stack(rows, cols, n, seed=3 * n, row0=row0, rows_total=rows + row0)
+    ax = orc.light_axis(g_step)
+    g = ax.size
+    p = rows * cols
+    d_f, d_c, d_ax = dev(torch, frames), dev(torch, cams), dev(torch, ax)
+    coef, bad = gpu_fit_frames(torch, frames, cams, row0=row0)
+    table = torch.empty((g, g, p), dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_table", coef.data_ptr(), p, p, d_ax.data_ptr(), g, table.data_ptr(), p, None, None)
+    coef2 = torch.empty_like(coef)
+    table2 = torch.full_like(table, -7)
+    bad2 = torch.zeros(2, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_table_frames", d_f.data_ptr(), p, d_c.data_ptr(), n, row0, rows, cols, d_ax.data_ptr(), g,
+               coef2.data_ptr(), p, table2.data_ptr(), p, bad2.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert bad == 0 and bad2.sum().item() == 0
+    assert torch.equal(coef, coef2)
+    assert torch.equal(table, table2)
+
+
+def test_fused_kernel_reference_golden(torch_cuda, ref_small):
+    from rti_b200 import _capi
+    torch = torch_cuda
+    frames, cams = ref_small["frames"], ref_small["cams"]
+    n, rows, cols = frames.shape
+    p = rows * cols
+    d_f, d_c, d_ax = dev(torch, frames), dev(torch, cams), dev(torch, orc.light_axis())
+    table = torch.empty((100, 100, p), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(2, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_table_frames", d_f.data_ptr(), p, d_c.data_ptr(), n, 0, rows, cols, d_ax.data_ptr(), 100,
+               None, 0, table.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert bad.sum().item() == 0
+    assert np.array_equal(table.cpu().numpy().reshape(100, 100, rows, cols), ref_small["table_ptm"])
