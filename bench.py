@@ -301,183 +301,21 @@ def run_gpu(args, rank, local_rank, world):
     if rank != 0:
         return
 
-    # ---- roofline of the (single) kernel of the step: HBM-bound on the table write
+    # ---- roofline of the step's kernel (gather + fit + table fused): HBM-bound on the table write
     peak, peak_src = read_peaks()
     alg_bytes = table_bytes + units_per_rank + 48 * p        # int32 table + uint8 frames + coefficient map
     achieved = alg_bytes / (fused_ms * 1e-3) / 1e9
+    tbl_bytes = table_bytes + 48 * p
     roofline = {"bound": "hbm", "kernel": "ptm_fused_kernel<true>", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": read_traffic(), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": fused_ms,
                 "two_kernel_form": {
-                    "ptm_fit_frames_kernel": {"launch_ms": fit_ms, "bound": "fp64 / conversion pipes",
+                    "ptm_fit_frames_kernel": {"launch_ms": fit_ms, "bound": "fp64 pipe",
+                                              "units_per_launch": units_per_rank,
                                               "gunits_per_s": units_per_rank / (fit_ms * 1e-3) / 1e9},
                     "ptm_table_kernel<4>": {"launch_ms": table_ms, "bound": "hbm",
-                                            "achieved": (table_bytes + 48 * p) / (table_ms * 1e-3) / 1e9,
-                                            "frac": (table_bytes + 48 * p) / (table_ms * 1e-3) / 1e9 / peak}}}
-
-    line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "rows": ROWS, "cols": COLS, "lights": N_LIGHTS, "grid": [G, G]},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0,
-    }
-    print(json.dumps(line), flush=True)
-
-
-# ------------------------------------------------------------------------------ GPU arm
-def run_gpu(args, rank, local_rank, world):
-    import torch
-    import rti_b200
-    from rti_b200 import _capi, synthetic
-
-    cpu = None
-    if world == 1 and not args.no_cpu_baseline:       # before CUDA is initialised: the pool forks
-        v, cores, sample, _ = cpu_reference(args.cpu_pixels_per_core)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
-
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    lib = _capi.load()
-    rows_total = ROWS * world
-    row0 = ROWS * rank
-    p = ROWS * COLS
-    units_per_rank = p * N_LIGHTS
-
-    # synthetic inputs: uniform-random uint8 frames of this rank's slab, shared camera track
-    frames, cams = synthetic.random_stack(ROWS, COLS, N_LIGHTS, seed=1 + rank, rows_total=rows_total)
-    cams = synthetic.camera_positions(rows_total, COLS, N_LIGHTS, np.random.default_rng(0))
-    axis = rti_b200.light_axis(0.02)
-    h_frames = torch.from_numpy(frames).pin_memory()
-    d_frames = h_frames.cuda()
-    d_cams = torch.from_numpy(cams).cuda()
-    d_axis = torch.from_numpy(axis).cuda()
-    d_coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
-    d_table = torch.empty((G, G, p), dtype=torch.int32, device="cuda")          # 42 GB
-    d_bad = torch.zeros(2, dtype=torch.int32, device="cuda")
-    stream = torch.cuda.current_stream().cuda_stream
-
-    def step():
-        # one fused kernel: gather + fit + table (the two-kernel form is timed below for comparison)
-        _capi.call("rti_ptm_fit_table_frames", d_frames.data_ptr(), p, d_cams.data_ptr(), N_LIGHTS, row0, ROWS, COLS,
-                   d_axis.data_ptr(), G, d_coef.data_ptr(), p, d_table.data_ptr(), p, d_bad.data_ptr(), stream)
-
-    def step_two_kernels():
-        _capi.call("rti_ptm_fit_frames", d_frames.data_ptr(), p, d_cams.data_ptr(), N_LIGHTS, row0, ROWS, COLS,
-                   d_coef.data_ptr(), p, d_bad.data_ptr(), stream)
-        _capi.call("rti_ptm_table", d_coef.data_ptr(), p, p, d_axis.data_ptr(), G, d_table.data_ptr(), p,
-                   d_bad.data_ptr() + 4, stream)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(args.warmup):
-        step()
-    barrier()
-    assert d_bad.sum().item() == 0, "singular / unrepresentable pixels in the synthetic workload"
-    d_bad.zero_()
-
-    # two-kernel form (untimed region, for the comparison printed under "kernel_ms")
-    ev2 = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-    step_two_kernels()
-    ev2[0].record()
-    _capi.call("rti_ptm_fit_frames", d_frames.data_ptr(), p, d_cams.data_ptr(), N_LIGHTS, row0, ROWS, COLS,
-               d_coef.data_ptr(), p, d_bad.data_ptr(), stream)
-    ev2[1].record()
-    _capi.call("rti_ptm_table", d_coef.data_ptr(), p, p, d_axis.data_ptr(), G, d_table.data_ptr(), p,
-               d_bad.data_ptr() + 4, stream)
-    ev2[2].record()
-    barrier()
-    fit_ms, table_ms = ev2[0].elapsed_time(ev2[1]), ev2[1].elapsed_time(ev2[2])
-
-    # ---- timed region: exactly K steps, device-timed, per-launch events for the roofline
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(args.steps)]
-    sampler = ClockSampler(local_rank)
-    lib.rti_launch_count(1)
-    sampler.start()
-    barrier()
-    t_start = torch.cuda.Event(enable_timing=True)
-    t_end = torch.cuda.Event(enable_timing=True)
-    t_start.record()
-    for k in range(args.steps):
-        ev[k][0].record()
-        step()
-        ev[k][1].record()
-    t_end.record()
-    barrier()
-    clocks = sampler.stop()
-    launches = int(lib.rti_launch_count(0))
-    total_ms = t_start.elapsed_time(t_end)
-    fused_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in ev]))
-    if dist is not None:
-        t = torch.tensor([total_ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms = float(t.item())
-    ms_per_step = total_ms / args.steps
-    value = units_per_rank * world / (ms_per_step * 1e-3) / 1e6
-
-    # ---- e2e: the host-buffer C-ABI call, H2D of the frames and D2H of the table inside
-    e2e = None
-    table_bytes = G * G * p * 4
-    if not args.no_e2e:
-        del d_table
-        torch.cuda.empty_cache()
-        try:
-            import psutil
-            avail = psutil.virtual_memory().available
-        except Exception:
-            avail = 1 << 62
-        if avail < world * table_bytes * 1.3:
-            e2e = {"value": None, "unit": UNIT, "skipped": "host RAM: %.0f GB available, need %.0f GB pinned"
-                   % (avail / 1e9, world * table_bytes / 1e9)}
-        else:
-            h_table = torch.empty((G, G, p), dtype=torch.int32, pin_memory=True)
-            h_cams = torch.from_numpy(cams)
-
-            def host_step():
-                _capi.call("rti_ptm_compute_host", h_frames.data_ptr(), h_cams.data_ptr(), N_LIGHTS, ROWS, COLS,
-                           0, ROWS, axis.ctypes.data, G, h_table.data_ptr(), None, 0)
-
-            # the slab's global row offset only shifts y; rti_ptm_compute_host takes row0 within the
-            # host frame buffer, so ranks pass their slab as a whole ROI of ROWS rows here
-            host_step()                                                  # warm-up (allocates the workspace)
-            barrier()
-            t0 = time.perf_counter()
-            for _ in range(args.e2e_steps):
-                host_step()
-            barrier()
-            dt = (time.perf_counter() - t0) / args.e2e_steps
-            if dist is not None:
-                t = torch.tensor([dt], dtype=torch.float64, device="cuda")
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                dt = float(t.item())
-            e2e = {"value": units_per_rank * world / dt / 1e6, "unit": UNIT,
-                   "h2d_bytes_per_step": int(frames.nbytes + cams.nbytes + axis.nbytes),
-                   "d2h_bytes_per_step": int(table_bytes), "ms_per_step": dt * 1e3, "steps": args.e2e_steps,
-                   "api": "rti_ptm_compute_host (pinned host frames -> int32 table in pinned host memory)"}
-            lib.rti_destroy()
-
-    if rank != 0:
-        return
-
-    # ---- roofline of the dominant kernel (the table write)
-    peak, peak_src = read_peaks()
-    alg_bytes = table_bytes + 48 * p                                     # int32 table + one coefficient read
-    achieved = alg_bytes / (table_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "ptm_table_kernel<4>", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": read_traffic(), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": table_ms,
-                "other_kernels": {"ptm_fit_frames_kernel": {
-                    "launch_ms": fit_ms, "bound": "fp64 pipe", "units_per_launch": units_per_rank,
-                    "gunits_per_s": units_per_rank / (fit_ms * 1e-3) / 1e9,
-                    "hbm_gbs": (units_per_rank + 48 * p) / (fit_ms * 1e-3) / 1e9}}}
+                                            "achieved": tbl_bytes / (table_ms * 1e-3) / 1e9,
+                                            "frac": tbl_bytes / (table_ms * 1e-3) / 1e9 / peak}}}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
