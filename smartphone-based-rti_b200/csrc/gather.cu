@@ -34,6 +34,25 @@ gather_soa_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
     const int64_t pix0 = (int64_t)blockIdx.x * G_PIX;
     const int f0 = blockIdx.y * G_FRAMES;
     const int fc = min(G_FRAMES, n - f0);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int QPW = 32 / (G_THREADS / 32);          // frame quads per warp (4)
+
+    // ---- phase 1a: all 16 byte loads of this thread are issued before anything waits on
+    // them (each warp load is one fully used 32-byte sector; 16 sectors in flight per warp)
+    const int64_t p = pix0 + lane;
+    const int64_t pc = p < n_pixels ? p : n_pixels - 1;
+    const int yl = (int)(pc / cols);
+    const double xd = (double)(int)(pc - (int64_t)yl * cols);
+    const double yd = (double)(row0 + yl);
+    const uint8_t *src = frames + pc;
+    uint8_t raw[QPW][4];
+#pragma unroll
+    for (int i = 0; i < QPW; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int f = (warp + i * (G_THREADS / 32)) * 4 + j;
+            raw[i][j] = f < fc ? __ldg(src + (int64_t)(f0 + f) * frame_stride) : (uint8_t)0;
+        }
     for (int i = threadIdx.x; i < fc; i += G_THREADS) {
         const double cz = cams[(int64_t)(f0 + i) * 3 + 2];
         s_cam[i][0] = cams[(int64_t)(f0 + i) * 3 + 0];
@@ -42,47 +61,33 @@ gather_soa_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
     }
     __syncthreads();
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    {   // ---- phase 1
-        const int64_t p = pix0 + lane;
-        const int64_t pc = p < n_pixels ? p : n_pixels - 1;
-        const int yl = (int)(pc / cols);
-        const double xd = (double)(int)(pc - (int64_t)yl * cols);
-        const double yd = (double)(row0 + yl);
-        const uint8_t *src = frames + pc;
-        for (int q = warp; q < 32; q += G_THREADS / 32) {
-            float ux[4], uy[4];
-            int iv[4];
-            uint8_t raw[4];
+    // ---- phase 1b: light vectors in fp64, parked as float4/int4 chunks
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int f = q * 4 + j;
-                raw[j] = f < fc ? __ldg(src + (int64_t)(f0 + f) * frame_stride) : (uint8_t)0;
-            }
+    for (int i = 0; i < QPW; ++i) {
+        const int q = warp + i * (G_THREADS / 32);
+        float ux[4], uy[4];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int f = min(q * 4 + j, fc - 1);
-                light_vector(s_cam[f][0], s_cam[f][1], s_cam[f][2], xd, yd, ux[j], uy[j]);
-                iv[j] = raw[j];
-            }
-            const int slot = lane * 32 + (q ^ lane);
-            s_lx[slot] = make_float4(ux[0], ux[1], ux[2], ux[3]);
-            s_ly[slot] = make_float4(uy[0], uy[1], uy[2], uy[3]);
-            s_in[slot] = make_int4(iv[0], iv[1], iv[2], iv[3]);
+        for (int j = 0; j < 4; ++j) {
+            const int f = min(q * 4 + j, fc - 1);
+            light_vector(s_cam[f][0], s_cam[f][1], s_cam[f][2], xd, yd, ux[j], uy[j]);
         }
+        const int slot = lane * 32 + (q ^ lane);
+        s_lx[slot] = make_float4(ux[0], ux[1], ux[2], ux[3]);
+        s_ly[slot] = make_float4(uy[0], uy[1], uy[2], uy[3]);
+        s_in[slot] = make_int4(raw[i][0], raw[i][1], raw[i][2], raw[i][3]);
     }
     __syncthreads();
     {   // ---- phase 2: lane = frame quad
         const int q = lane;
         const int f = f0 + q * 4;
         for (int pl = warp; pl < G_PIX; pl += G_THREADS / 32) {
-            const int64_t p = pix0 + pl;
-            if (p >= n_pixels) break;
+            const int64_t po = pix0 + pl;
+            if (po >= n_pixels) break;
             const int slot = pl * 32 + (q ^ pl);
             const float4 a = s_lx[slot];
             const float4 b = s_ly[slot];
             const int4 c = s_in[slot];
-            const int64_t o = p * n + f;
+            const int64_t o = po * n + f;
             if (VEC && f + 3 < n) {
                 __stcs(reinterpret_cast<float4 *>(lx + o), a);
                 __stcs(reinterpret_cast<float4 *>(ly + o), b);

@@ -71,59 +71,110 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
 
 // --------------------------------------------------------------------------------------
 // Fit from materialised (lx, ly, intensity) arrays [pixel][n], light index fastest
-// (the compute_intensities layout, analysis.py:217-219).  One warp per pixel: lanes
-// stride the light axis so every load is a coalesced 128-byte line, the 26 partial
-// sums are combined with warp shuffles and lane 0 does the in-register Cholesky.
-// Bound: HBM (12 bytes per pixel.light).
+// (the compute_intensities layout, analysis.py:217-219).
+// A CTA owns 128 consecutive pixels, one per thread.  The three arrays are streamed through
+// shared memory in stages of 32 lights with cp.async (16-byte chunks: 8 consecutive threads
+// fetch one pixel's 128-byte line, so global reads are whole lines), double buffered.  Chunk
+// c of row t lives at chunk position c ^ (t & 7): the cp.async writes and the per-thread
+// LDS.128 reads (row = thread) are both bank-conflict free.  Every thread then owns its
+// pixel's 26 running sums: no cross-lane reduction, and the 6x6 solves run on all lanes.
+// Lights past n and pixels past n_pixels are zero-filled by cp.async (src-size 0), which
+// adds exact zeros to the sums.
+// Bound: 12 B of HBM per pixel.light against 32 fp64 issue slots + 6 conversions; at full
+// fp64 rate that is ~7 TB/s, i.e. the kernel sits at the HBM / fp64 ridge.
 // --------------------------------------------------------------------------------------
-constexpr int SOA_WARPS = 8;
+constexpr int SOA_PIX = 128;                 // pixels per CTA = threads per CTA
+constexpr int SOA_KL = 32;                   // lights per stage (one 128-byte line per array and pixel)
+constexpr int SOA_ARRAY_BYTES = SOA_PIX * SOA_KL * 4;            // 16 KB
+constexpr int SOA_STAGE_BYTES = 3 * SOA_ARRAY_BYTES;             // 48 KB
+constexpr size_t SOA_SMEM = 2 * SOA_STAGE_BYTES;                 // 96 KB -> 2 CTAs per SM
 
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+__device__ __forceinline__ void cp_async_zfill(void *smem, const void *gmem, int bytes, int src_bytes) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    if (bytes == 16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem), "r"(src_bytes));
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(s), "l"(gmem), "r"(src_bytes));
 }
 
-__global__ void __launch_bounds__(SOA_WARPS * 32)
+template <bool VEC16>
+__global__ void __launch_bounds__(SOA_PIX, 2)
 ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
                    const int32_t *__restrict__ inten, int64_t n_pixels, int n,
                    double *__restrict__ coef, int64_t plane_stride, int32_t *__restrict__ bad) {
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = (int64_t)blockIdx.x * SOA_WARPS + (threadIdx.x >> 5);
-    const int64_t n_warps = (int64_t)gridDim.x * SOA_WARPS;
-    for (int64_t p = warp; p < n_pixels; p += n_warps) {
-        const float *px = lx + p * n;
-        const float *py = ly + p * n;
-        const int32_t *pi = inten + p * n;
-        NormalEq ne;
-        ne.clear();
-        int i = lane;
-        for (; i + 96 < n; i += 128) {                     // 4 independent lines in flight
-            float u[4], v[4];
-            int w[4];
+    extern __shared__ __align__(16) unsigned char s_soa[];
+    const int t = threadIdx.x;
+    const int64_t p0 = (int64_t)blockIdx.x * SOA_PIX;
+    const void *base[3] = {lx, ly, inten};
+
+    auto issue = [&](int stage, int i0) {
+        unsigned char *dst0 = s_soa + stage * SOA_STAGE_BYTES;
+        if (VEC16) {
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                u[j] = __ldcs(px + i + 32 * j);
-                v[j] = __ldcs(py + i + 32 * j);
-                w[j] = __ldcs(pi + i + 32 * j);
+            for (int it = 0; it < 3 * SOA_PIX * 8 / SOA_PIX; ++it) {
+                const int idx = it * SOA_PIX + t;
+                const int a = it / 8;                              // 1024 chunks per array, 128 per `it`
+                const int rem = idx - a * (SOA_PIX * 8);
+                const int row = rem >> 3, c = rem & 7;
+                const int64_t p = p0 + row;
+                const int light = i0 + 4 * c;
+                int nb = (p < n_pixels) ? (n - light) * 4 : 0;
+                nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
+                const char *src = reinterpret_cast<const char *>(base[a]);
+                if (nb > 0) src += (p * n + light) * 4;
+                cp_async_zfill(dst0 + a * SOA_ARRAY_BYTES + row * 128 + ((c ^ (row & 7)) << 4), src, 16, nb);
             }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) ne.add(u[j], v[j], (double)w[j]);
+        } else {
+            for (int it = 0; it < 3 * SOA_KL; ++it) {
+                const int idx = it * SOA_PIX + t;
+                const int a = it / SOA_KL;
+                const int rem = idx - a * (SOA_PIX * SOA_KL);
+                const int row = rem >> 5, w = rem & 31;
+                const int64_t p = p0 + row;
+                const int light = i0 + w;
+                const int nb = (p < n_pixels && light < n) ? 4 : 0;
+                const char *src = reinterpret_cast<const char *>(base[a]);
+                if (nb > 0) src += (p * n + light) * 4;
+                cp_async_zfill(dst0 + a * SOA_ARRAY_BYTES + row * 128 + (((w >> 2) ^ (row & 7)) << 4) + ((w & 3) << 2),
+                               src, 4, nb);
+            }
         }
-        for (; i < n; i += 32) ne.add(__ldcs(px + i), __ldcs(py + i), (double)__ldcs(pi + i));
-#pragma unroll
-        for (int k = 0; k < 15; ++k) ne.g[k] = warp_sum(ne.g[k]);
-#pragma unroll
-        for (int k = 0; k < 5; ++k) ne.s[k] = warp_sum(ne.s[k]);
-#pragma unroll
-        for (int k = 0; k < 6; ++k) ne.r[k] = warp_sum(ne.r[k]);
-        if (lane == 0) {
-            double a[6];
-            const bool ok = solve_normal_eq(ne, (double)n, a);
-#pragma unroll
-            for (int k = 0; k < 6; ++k) coef[k * plane_stride + p] = a[k];
-            if (!ok && bad != nullptr) atomicAdd(bad, 1);
+        asm volatile("cp.async.commit_group;\n" ::);
+    };
+
+    NormalEq ne;
+    ne.clear();
+    const int n_stages = (n + SOA_KL - 1) / SOA_KL;
+    issue(0, 0);
+    for (int s = 0; s < n_stages; ++s) {
+        if (s + 1 < n_stages) {
+            issue((s + 1) & 1, (s + 1) * SOA_KL);
+            asm volatile("cp.async.wait_group 1;\n" ::);
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::);
         }
+        __syncthreads();
+        const unsigned char *row = s_soa + (s & 1) * SOA_STAGE_BYTES + t * 128;
+#pragma unroll 2
+        for (int c = 0; c < 8; ++c) {
+            const int off = (c ^ (t & 7)) << 4;
+            const float4 u = *reinterpret_cast<const float4 *>(row + off);
+            const float4 v = *reinterpret_cast<const float4 *>(row + SOA_ARRAY_BYTES + off);
+            const int4 w = *reinterpret_cast<const int4 *>(row + 2 * SOA_ARRAY_BYTES + off);
+            ne.add(u.x, v.x, (double)w.x);
+            ne.add(u.y, v.y, (double)w.y);
+            ne.add(u.z, v.z, (double)w.z);
+            ne.add(u.w, v.w, (double)w.w);
+        }
+        __syncthreads();                     // buffer s & 1 is refilled by the next iteration's issue
+    }
+    const int64_t p = p0 + t;
+    double a[6];
+    const bool ok = solve_normal_eq(ne, (double)n, a);
+    if (p < n_pixels) {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) coef[k * plane_stride + p] = a[k];
+        if (!ok && bad != nullptr) atomicAdd(bad, 1);
     }
 }
 
@@ -214,11 +265,19 @@ extern "C" int rti_ptm_fit_soa(const float *d_lx, const float *d_ly, const int32
         return n <= 0 ? RTI_ERR_ARG : RTI_ERR_TOO_FEW;
     }
     RTI_REQUIRE(plane_stride >= n_pixels, "rti_ptm_fit_soa: plane_stride < pixels");
-    int64_t blocks = (n_pixels + SOA_WARPS - 1) / SOA_WARPS;
-    const int64_t cap = 148LL * 8 * 16;                    // persistent-ish: 16 waves of 8 CTAs/SM
-    if (blocks > cap) blocks = cap;
-    ptm_fit_soa_kernel<<<(unsigned)blocks, SOA_WARPS * 32, 0, as_stream(stream)>>>(
-        d_lx, d_ly, d_inten, n_pixels, n, d_coef, plane_stride, d_bad);
+    const int64_t blocks = (n_pixels + SOA_PIX - 1) / SOA_PIX;
+    RTI_REQUIRE(blocks <= 0x7fffffffLL, "rti_ptm_fit_soa: too many pixels");
+    const bool vec16 = (n % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_lx) & 15) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(d_ly) & 15) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(d_inten) & 15) == 0);
+    RTI_CUDA(cudaFuncSetAttribute(ptm_fit_soa_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOA_SMEM));
+    RTI_CUDA(cudaFuncSetAttribute(ptm_fit_soa_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOA_SMEM));
+    if (vec16)
+        ptm_fit_soa_kernel<true><<<(unsigned)blocks, SOA_PIX, SOA_SMEM, as_stream(stream)>>>(
+            d_lx, d_ly, d_inten, n_pixels, n, d_coef, plane_stride, d_bad);
+    else
+        ptm_fit_soa_kernel<false><<<(unsigned)blocks, SOA_PIX, SOA_SMEM, as_stream(stream)>>>(
+            d_lx, d_ly, d_inten, n_pixels, n, d_coef, plane_stride, d_bad);
     RTI_LAUNCHED("ptm_fit_soa_kernel");
     return RTI_OK;
 }

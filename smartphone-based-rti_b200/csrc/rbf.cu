@@ -317,29 +317,47 @@ rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const
 
 // --------------------------------------------------------------------------------------
 // Grid evaluation: value(v, u) = sum_k |(axis[u], axis[v]) - n_k| * w_k  (Rbf.__call__).
-// A CTA owns PB consecutive pixels and a chunk of grid rows; a thread owns one direction
-// and accumulates all PB pixels, so that table stores are PB*4 contiguous bytes.  Node
-// data is staged in shared memory chunk by chunk and read as broadcasts.
-// Bound: fp64 pipe (~10 issue slots per pixel.direction.node).
+// A CTA owns PB consecutive pixels and EV_THREADS strips of EV_U consecutive directions of
+// one grid row; a thread owns one strip, so (gy - y_k)^2 is shared by its EV_U directions
+// and a node costs 3 broadcast LDS per 2 + 6*EV_U fp64 instructions.  Per term:
+//     dx = gx - x_k;  d2 = dx*dx + dy2;  r = MUFU.RSQ64H(d2) (2^-22.9);  t = d2*r;
+//     q = 3 - t*r;    acc += (t*q) * (w_k/2)          [= w_k sqrt(d2) (1 - 1.5 delta^2)]
+// i.e. 6 fp64 issue slots and one MUFU, relative error 2.4e-14 per distance.  dy2 carries
+// +1e-300 so that a grid point that coincides with a node gives t = 1e-150 instead of 0*inf.
+// Table stores are PB*4 contiguous bytes per direction (one 32 B sector for PB = 8); the
+// kernel is fp64-pipe bound: the table write is 4 B per N*6.5 fp64 slots.
 // --------------------------------------------------------------------------------------
 constexpr int EV_THREADS = 256;
 constexpr int EV_KCH = 128;             // nodes staged per chunk
+constexpr int EV_U = 4;                 // directions per thread (one strip of a grid row)
+
+__device__ __forceinline__ double rsq64h(double d2) {
+    double r;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d2));
+    return r;
+}
 
 template <int PB, bool TABLE>
 __global__ void __launch_bounds__(EV_THREADS)
 rbf_eval_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const double *__restrict__ weights,
-                int64_t n_pixels, int n, const double *__restrict__ axis, int g, void *__restrict__ out,
-                int64_t image_stride, int32_t *__restrict__ bad) {
+                int64_t n_pixels, int n, const double *__restrict__ axis, int g, int strips_per_row,
+                void *__restrict__ out, int64_t image_stride, int32_t *__restrict__ bad) {
     __shared__ double s_x[PB][EV_KCH], s_y[PB][EV_KCH], s_w[PB][EV_KCH];
     const int64_t p0 = (int64_t)blockIdx.x * PB;
-    const int64_t gg = (int64_t)g * g;
-    const int64_t d = (int64_t)blockIdx.y * EV_THREADS + threadIdx.x;        // direction index v*g + u
-    const bool live = d < gg;
-    const int v = live ? (int)(d / g) : 0, u = live ? (int)(d - (int64_t)v * g) : 0;
-    const double gx = axis[u], gy = axis[v];
-    double acc[PB];
+    const int strip = blockIdx.y * EV_THREADS + threadIdx.x;
+    const bool live = strip < strips_per_row * g;
+    const int v = live ? strip / strips_per_row : 0;
+    const int u0 = live ? (strip - v * strips_per_row) * EV_U : 0;
+    double gx[EV_U];
 #pragma unroll
-    for (int q = 0; q < PB; ++q) acc[q] = 0.0;
+    for (int j = 0; j < EV_U; ++j) gx[j] = axis[min(u0 + j, g - 1)];
+    const double gy = axis[v];
+    double acc[PB][EV_U];
+#pragma unroll
+    for (int q = 0; q < PB; ++q)
+#pragma unroll
+        for (int j = 0; j < EV_U; ++j) acc[q][j] = 0.0;
+
     for (int k0 = 0; k0 < n; k0 += EV_KCH) {
         const int kc = min(EV_KCH, n - k0);
         __syncthreads();
@@ -348,41 +366,60 @@ rbf_eval_kernel(const float *__restrict__ lx, const float *__restrict__ ly, cons
             const int64_t p = (p0 + q < n_pixels) ? p0 + q : n_pixels - 1;
             s_x[q][k] = (double)lx[p * n + k0 + k];
             s_y[q][k] = (double)ly[p * n + k0 + k];
-            s_w[q][k] = weights[p * n + k0 + k];
+            s_w[q][k] = 0.5 * weights[p * n + k0 + k];
         }
         __syncthreads();
 #pragma unroll
         for (int q = 0; q < PB; ++q) {
-            double a = acc[q];
-#pragma unroll 4
+#pragma unroll 2
             for (int k = 0; k < kc; ++k) {
-                const double dx = gx - s_x[q][k], dy = gy - s_y[q][k];
-                const double d2 = fma(dx, dx, dy * dy);
-                // one Newton step on the MUFU seed: relative error ~1e-13
-                // (the clamp keeps the seed finite when d2 == 0: then d2 * r == 0 exactly)
-                double r = (double)rsqrtf(fmaxf((float)d2, 1e-30f));
-                r = r * fma(-(0.5 * d2) * r, r, 1.5);
-                a = fma(d2 * r, s_w[q][k], a);
+                const double xk = s_x[q][k], wk = s_w[q][k];
+                const double dy = gy - s_y[q][k];
+                const double dy2 = fma(dy, dy, 1e-300);
+#pragma unroll
+                for (int j = 0; j < EV_U; ++j) {
+                    const double dx = gx[j] - xk;
+                    const double d2 = fma(dx, dx, dy2);
+                    const double r = rsq64h(d2);
+                    const double t = d2 * r;
+                    const double c = fma(-t, r, 3.0);
+                    acc[q][j] = fma(t * c, wk, acc[q][j]);
+                }
             }
-            acc[q] = a;
         }
     }
     if (!live) return;
     bool any_bad = false;
-    if (TABLE) {
-        int32_t *dst = reinterpret_cast<int32_t *>(out) + d * image_stride + p0;
 #pragma unroll
-        for (int q = 0; q < PB; ++q) {
-            if (p0 + q < n_pixels) {
-                if (!(fabs(acc[q]) < 2147483648.0)) any_bad = true;
-                dst[q] = trunc_i32(acc[q]);
+    for (int j = 0; j < EV_U; ++j) {
+        if (u0 + j >= g) break;
+        const int64_t d = (int64_t)v * g + u0 + j;
+        if (TABLE) {
+            int32_t *dst = reinterpret_cast<int32_t *>(out) + d * image_stride + p0;
+            if (PB == 8 && p0 + PB <= n_pixels && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                int val[PB];
+#pragma unroll
+                for (int q = 0; q < PB; ++q) {
+                    if (!(fabs(acc[q][j]) < 2147483648.0)) any_bad = true;
+                    val[q] = trunc_i32(acc[q][j]);
+                }
+                __stcs(reinterpret_cast<int4 *>(dst), make_int4(val[0], val[1], val[2], val[3]));
+                __stcs(reinterpret_cast<int4 *>(dst) + 1, make_int4(val[4 % PB], val[5 % PB], val[6 % PB], val[7 % PB]));
+            } else {
+#pragma unroll
+                for (int q = 0; q < PB; ++q) {
+                    if (p0 + q < n_pixels) {
+                        if (!(fabs(acc[q][j]) < 2147483648.0)) any_bad = true;
+                        dst[q] = trunc_i32(acc[q][j]);
+                    }
+                }
             }
-        }
-    } else {
-        double *dst = reinterpret_cast<double *>(out);
+        } else {
+            double *dst = reinterpret_cast<double *>(out);
 #pragma unroll
-        for (int q = 0; q < PB; ++q)
-            if (p0 + q < n_pixels) dst[(p0 + q) * gg + d] = acc[q];
+            for (int q = 0; q < PB; ++q)
+                if (p0 + q < n_pixels) dst[(p0 + q) * (int64_t)g * g + d] = acc[q][j];
+        }
     }
     if (any_bad && bad != nullptr) atomicAdd(bad, 1);
 }
@@ -427,18 +464,18 @@ static int rbf_eval_launch(const float *d_lx, const float *d_ly, const double *d
                            rti_stream_t stream, const char *who) {
     RTI_REQUIRE(d_lx && d_ly && d_weights && d_axis && d_out, "%s: NULL pointer", who);
     RTI_REQUIRE(n_pixels > 0 && n > 0 && g > 0 && g <= 2048, "%s: bad sizes", who);
-    const int64_t gg = (int64_t)g * g;
-    const unsigned gy = (unsigned)((gg + EV_THREADS - 1) / EV_THREADS);
+    const int strips_per_row = (g + EV_U - 1) / EV_U;
+    const unsigned gy = (unsigned)(((int64_t)strips_per_row * g + EV_THREADS - 1) / EV_THREADS);
     if (TABLE) {
         RTI_REQUIRE(image_stride >= n_pixels, "%s: image_stride < pixels", who);
         const int64_t bx = (n_pixels + 7) / 8;
         RTI_REQUIRE(bx <= 0x7fffffffLL, "%s: too many pixels", who);
         rbf_eval_kernel<8, true><<<dim3((unsigned)bx, gy), EV_THREADS, 0, as_stream(stream)>>>(
-            d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_out, image_stride, d_bad);
+            d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, strips_per_row, d_out, image_stride, d_bad);
     } else {
         RTI_REQUIRE(n_pixels <= 0x7fffffffLL, "%s: too many pixels", who);
         rbf_eval_kernel<1, false><<<dim3((unsigned)n_pixels, gy), EV_THREADS, 0, as_stream(stream)>>>(
-            d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_out, 0, d_bad);
+            d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, strips_per_row, d_out, 0, d_bad);
     }
     RTI_LAUNCHED("rbf_eval_kernel");
     return RTI_OK;
