@@ -21,8 +21,12 @@
 namespace rti {
 
 constexpr int TS = 64;                  // tile edge
-constexpr int KC = 32;                  // k-chunk depth of one staged operand block
+constexpr int KC = 32;                  // k-rows per 16 KB block of the L workspace
 constexpr int BLK = KC * TS;            // doubles per block (16 KB)
+constexpr int KS = 16;                  // k-rows staged per pipeline stage
+constexpr int LDS = TS + 4;             // leading dimension of staged operands: the 4 k-rows of a DMMA
+                                        // fragment land in disjoint bank groups (68*2 mod 32 = 8)
+constexpr int STG = KS * LDS;           // doubles per staged operand chunk
 constexpr int RBF_THREADS = 256;
 constexpr int SD_LD = TS + 1;           // padded leading dimension of the potrf scratch
 
@@ -39,21 +43,34 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // |d| for d2 >= 0 in fp64 (MUFU seed + Newton, ~2 ulp); 0 for d2 == 0
 __device__ __forceinline__ double sqrt_pos(double d2) { return d2 > 0.0 ? d2 * rsqrt_pos(d2) : 0.0; }
 
-// acc[i][j] -= sum_k A[k][r0+i] * B[k][c0+j] over one staged chunk of `depth` k-rows
-__device__ __forceinline__ void mma_chunk(double (&acc)[4][4], const double *__restrict__ sA,
-                                          const double *__restrict__ sB, int r0, int c0, int depth) {
+// fp64 tensor-core step: D(8x8) += A(8x4) . B(4x8), mma.sync.m8n8k4 (DMMA).  Lane l holds
+// A[l>>2][l&3], B[l&3][l>>2] and D[l>>2][2*(l&3) + {0,1}].  Measured on B200: 18.5 T FMA/s
+// against 16.8 T for DFMA chains (tools/peak_fp64.cu), with 1/8 of the issue slots and 1/8 of
+// the shared-memory operand traffic of a 4x4 register-tiled DFMA micro-kernel.
+__device__ __forceinline__ void dmma(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// A warp owns a 16 x 32 patch of the 64 x 64 tile: 2 x 4 DMMA tiles, acc[mi][ni][e] is element
+// (rw + 8*mi + (lane>>2), cw + 8*ni + 2*(lane&3) + e).
+// acc -= sum_k A[k][row] * B[k][col] over `depth` staged k-rows (operands [k][LD], k-major).
+template <int LD>
+__device__ __forceinline__ void mma_chunk(double (&acc)[2][4][2], const double *__restrict__ sA,
+                                          const double *__restrict__ sB, int rw, int cw, int lane, int depth) {
+    const double *pa = sA + (lane & 3) * LD + rw + (lane >> 2);
+    const double *pb = sB + (lane & 3) * LD + cw + (lane >> 2);
 #pragma unroll 4
-    for (int k = 0; k < depth; ++k) {
-        const double2 a01 = *reinterpret_cast<const double2 *>(sA + k * TS + r0);
-        const double2 a23 = *reinterpret_cast<const double2 *>(sA + k * TS + r0 + 2);
-        const double2 b01 = *reinterpret_cast<const double2 *>(sB + k * TS + c0);
-        const double2 b23 = *reinterpret_cast<const double2 *>(sB + k * TS + c0 + 2);
-        const double a[4] = {a01.x, a01.y, a23.x, a23.y};
-        const double b[4] = {b01.x, b01.y, b23.x, b23.y};
+    for (int k = 0; k < depth; k += 4) {
+        double a[2], b[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i)
+        for (int mi = 0; mi < 2; ++mi) a[mi] = -pa[k * LD + 8 * mi];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) acc[i][j] = fma(-a[i], b[j], acc[i][j]);
+        for (int ni = 0; ni < 4; ++ni) b[ni] = pb[k * LD + 8 * ni];
+#pragma unroll
+        for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) dmma(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
     }
 }
 
@@ -69,20 +86,21 @@ __device__ __forceinline__ double block_sum(double v, double *s_red) {
     return t;
 }
 
-// Shared memory map (doubles):  [0, 4096) sA (2 chunk buffers)   [4096, 8192) sB (2 chunk buffers)
-//   the potrf scratch sD[64][65], the transposed C tile and the substitution vectors alias sA/sB
-//   [8192, 12288) sW = D^-T of the current block column   then sRsq[64], s_red[8], nodes (4 * n)
+// Shared memory map (doubles):  [0, 2*STG) sA (2 stages)   [2*STG, 4*STG) sB (2 stages)
+//   the potrf scratch sD[64][65] and the transposed C tile sCk[64][LDS] alias sA/sB, as do the
+//   substitution vectors;  [4*STG, 4*STG + 64*LDS) sW = D^-T of the current block column
+//   then sRsq[64], s_red[8], nodes (4 * n).  102 KB at n = 1000: two CTAs per SM.
 __global__ void __launch_bounds__(RBF_THREADS, 2)
 rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const int32_t *__restrict__ inten,
                int64_t n_pixels, int n, double *__restrict__ weights, double *__restrict__ work,
                int64_t work_stride, int32_t *__restrict__ bad) {
     extern __shared__ __align__(16) double smem[];
     double *sA = smem;
-    double *sB = smem + 2 * BLK;
+    double *sB = smem + 2 * STG;
     double *sD = smem;                          // alias: [64][65]
-    double *sCk = smem;                         // alias: [64 k][64 r]
-    double *sW = smem + 4 * BLK;                // [64 k][64 c]: sW[k][c] = Dinv[c][k]
-    double *sRsq = sW + TS * TS;
+    double *sCk = smem;                         // alias: [64 k][LDS]
+    double *sW = smem + 4 * STG;                // [64 k][LDS]: sW[k][c] = Dinv[c][k]
+    double *sRsq = sW + TS * LDS;
     double *s_red = sRsq + TS;
     double *sx = s_red + 8;
     double *sy = sx + n;
@@ -90,8 +108,10 @@ rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const
     double *sd = sa + n;
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int r0 = 16 * (warp >> 1) + 4 * (lane >> 3);          // micro-tile origin inside a 64x64 tile
-    const int c0 = 32 * (warp & 1) + 4 * (lane & 7);
+    const int rw = 16 * (warp >> 1);                            // warp patch origin inside a 64x64 tile
+    const int cw = 32 * (warp & 1);
+    const int er = rw + (lane >> 2);                            // element (mi, ni, e): row er + 8*mi,
+    const int ec = cw + 2 * (lane & 3);                         //                      col ec + 8*ni + e
     const int M = n - 1;
     const int mpad = rbf_mpad(n);
     const int nT = mpad / TS, nKC = mpad / KC;
@@ -116,35 +136,40 @@ rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const
         for (int kb = 0; kb < nT; ++kb) {
             for (int it = kb; it < nT; ++it) {
                 // ---- generate the tile of the bordered matrix in registers
-                double acc[4][4];
+                double acc[2][4][2];
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int gr = it * TS + r0 + i;
+                for (int mi = 0; mi < 2; ++mi) {
+                    const int gr = it * TS + er + 8 * mi;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int gc = kb * TS + c0 + j;
-                        double v;
-                        if (gc >= M) v = (gr == gc) ? 1.0 : 0.0;                    // padding: identity
-                        else if (gr < M) {
-                            const double dx = sx[gr + 1] - sx[gc + 1], dy = sy[gr + 1] - sy[gc + 1];
-                            v = sa[gr + 1] + sa[gc + 1] - sqrt_pos(fma(dx, dx, dy * dy));
-                        } else if (gr == M) v = sd[0] - sd[gc + 1];                 // rhs 1: d0*1 - d'
-                        else if (gr == M + 1) v = sa[gc + 1];                       // rhs 2: a
-                        else v = 0.0;
-                        acc[i][j] = v;
-                    }
+                    for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int gc = kb * TS + ec + 8 * ni + e;
+                            double v;
+                            if (gc >= M) v = (gr == gc) ? 1.0 : 0.0;                    // padding: identity
+                            else if (gr < M) {
+                                const double dx = sx[gr + 1] - sx[gc + 1], dy = sy[gr + 1] - sy[gc + 1];
+                                v = sa[gr + 1] + sa[gc + 1] - sqrt_pos(fma(dx, dx, dy * dy));
+                            } else if (gr == M) v = sd[0] - sd[gc + 1];                 // rhs 1: d0*1 - d'
+                            else if (gr == M + 1) v = sa[gc + 1];                       // rhs 2: a
+                            else v = 0.0;
+                            acc[mi][ni][e] = v;
+                        }
                 }
                 // ---- acc -= L[it][0:k0] . L[kb][0:k0]^T, operand chunks streamed with cp.async
-                const int nk = 2 * kb;
+                const int nk = kb * (TS / KS);
                 const bool diag = (it == kb);
+                // row block `it` of L is one contiguous [k][64] array of mpad k-rows
+                const double *ga = L + (int64_t)it * nKC * BLK;
+                const double *gb = L + (int64_t)kb * nKC * BLK;
                 auto issue = [&](int buf, int kc) {
-                    const double *ga = L + ((int64_t)it * nKC + kc) * BLK;
-                    const double *gb = L + ((int64_t)kb * nKC + kc) * BLK;
 #pragma unroll
-                    for (int i = 0; i < BLK * 8 / 16 / RBF_THREADS; ++i) {
-                        const int e = (t + i * RBF_THREADS) * 2;
-                        cp_async16(sA + buf * BLK + e, ga + e);
-                        if (!diag) cp_async16(sB + buf * BLK + e, gb + e);
+                    for (int i = 0; i < KS * TS * 8 / 16 / RBF_THREADS; ++i) {
+                        const int ch = t + i * RBF_THREADS;              // 16-byte chunk: k-row ch/32, doubles 2*(ch%32)
+                        const int so = (ch >> 5) * LDS + (ch & 31) * 2;
+                        const int64_t go = (int64_t)kc * KS * TS + ch * 2;
+                        cp_async16(sA + buf * STG + so, ga + go);
+                        if (!diag) cp_async16(sB + buf * STG + so, gb + go);
                     }
                     cp_async_commit();
                 };
@@ -154,20 +179,23 @@ rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const
                     if (kc + 1 < nk) { issue((kc + 1) & 1, kc + 1); cp_async_wait<1>(); }
                     else cp_async_wait<0>();
                     __syncthreads();
-                    const double *pa = sA + (kc & 1) * BLK;
-                    mma_chunk(acc, pa, diag ? pa : sB + (kc & 1) * BLK, r0, c0, KC);
+                    const double *pa = sA + (kc & 1) * STG;
+                    mma_chunk<LDS>(acc, pa, diag ? pa : sB + (kc & 1) * STG, rw, cw, lane, KS);
                     __syncthreads();
                 }
 
                 if (diag) {
                     // ---- potrf of the 64x64 diagonal tile in shared memory
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
+                    for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int gr = kb * TS + r0 + i, gc = kb * TS + c0 + j;
-                            sD[(r0 + i) * SD_LD + c0 + j] = (gc >= M) ? ((gr == gc) ? 1.0 : 0.0) : acc[i][j];
-                        }
+                        for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int r = er + 8 * mi, c = ec + 8 * ni + e;
+                                const int gr = kb * TS + r, gc = kb * TS + c;
+                                sD[r * SD_LD + c] = (gc >= M) ? ((gr == gc) ? 1.0 : 0.0) : acc[mi][ni][e];
+                            }
                     const int ur = t >> 2;                       // this thread updates row ur, columns uc0 + 4m
                     const int uc0 = t & 3;
                     for (int j = 0; j < TS; ++j) {
@@ -200,14 +228,14 @@ rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const
                         const int k = t >> 2, q = t & 3;
                         for (int c = 0; c < TS; ++c) {
                             double part = 0.0;
-                            for (int p = k + q; p < c; p += 4) part = fma(sD[c * SD_LD + p], sW[k * TS + p], part);
+                            for (int p = k + q; p < c; p += 4) part = fma(sD[c * SD_LD + p], sW[k * LDS + p], part);
                             part += __shfl_xor_sync(0xffffffffu, part, 1);
                             part += __shfl_xor_sync(0xffffffffu, part, 2);
                             double v;
                             if (c < k) v = 0.0;
                             else if (c == k) v = sRsq[c];                            // 1/D[k][k]
                             else v = -part * sRsq[c];                               // 1/D[c][c] = rsqrt(piv_c)
-                            if (q == 0) sW[k * TS + c] = v;
+                            if (q == 0) sW[k * LDS + c] = v;
                             __syncwarp();
                         }
                     }
@@ -217,31 +245,35 @@ rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const
                     for (int e = t; e < TS * TS; e += RBF_THREADS) {
                         const int c = e >> 6, r = e & 63;
                         gd[c * TS + r] = sD[r * SD_LD + c];                          // chunks 2kb, 2kb+1 are adjacent
-                        Wg[(int64_t)kb * TS * TS + e] = sW[e];
+                        Wg[(int64_t)kb * TS * TS + e] = sW[c * LDS + r];
                     }
                 } else {
                     // ---- X = C . D^-T through the same micro-kernel: A operand = C^T staged [k=c][r]
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
+                    for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const int gc = kb * TS + c0 + j, gr = it * TS + r0 + i;
-                            sCk[(c0 + j) * TS + r0 + i] = (gc >= M) ? ((gr == gc) ? 1.0 : 0.0) : acc[i][j];
-                        }
+                        for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int r = er + 8 * mi, c = ec + 8 * ni + e;
+                                const int gc = kb * TS + c, gr = it * TS + r;
+                                sCk[c * LDS + r] = (gc >= M) ? ((gr == gc) ? 1.0 : 0.0) : acc[mi][ni][e];
+                            }
                     __syncthreads();
-                    double x[4][4];
+                    double x[2][4][2];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
+                    for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) x[i][j] = 0.0;
-                    mma_chunk(x, sCk, sW, r0, c0, TS);                               // x = -C.D^-T
-                    double *gx = L + ((int64_t)it * nKC + 2 * kb) * BLK;
+                        for (int ni = 0; ni < 4; ++ni) x[mi][ni][0] = x[mi][ni][1] = 0.0;
+                    mma_chunk<LDS>(x, sCk, sW, rw, cw, lane, TS);                    // x = -C.D^-T
+                    double *gx = L + ((int64_t)it * nKC + 2 * kb) * BLK;             // [k = c][r], 64 k-rows
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        double *dst = gx + (c0 + j) * TS + r0;
-                        *reinterpret_cast<double2 *>(dst) = make_double2(-x[0][j], -x[1][j]);
-                        *reinterpret_cast<double2 *>(dst + 2) = make_double2(-x[2][j], -x[3][j]);
-                    }
+                    for (int mi = 0; mi < 2; ++mi)
+#pragma unroll
+                        for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e)
+                                gx[(ec + 8 * ni + e) * TS + er + 8 * mi] = -x[mi][ni][e];
                 }
             }
         }
@@ -429,7 +461,7 @@ rbf_eval_kernel(const float *__restrict__ lx, const float *__restrict__ ly, cons
 using namespace rti;
 
 static size_t rbf_fit_smem(int n) {
-    return (size_t)(4 * BLK + TS * TS + TS + 8 + 4 * n) * sizeof(double);
+    return (size_t)(4 * STG + TS * LDS + TS + 8 + 4 * n) * sizeof(double);
 }
 
 extern "C" int64_t rti_rbf_workspace_bytes(int n, int batch) {
@@ -448,6 +480,9 @@ extern "C" int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32
     RTI_REQUIRE(work_bytes >= rti_rbf_workspace_bytes(n, batch), "rti_rbf_fit_soa: workspace too small");
     RTI_REQUIRE((reinterpret_cast<uintptr_t>(d_work) & 15) == 0, "rti_rbf_fit_soa: workspace not 16-byte aligned");
     const size_t smem = rbf_fit_smem(n);
+    // the four substitution vectors of length mpad alias the operand stages and sW
+    RTI_REQUIRE(4 * rbf_mpad(n) <= 4 * STG + TS * LDS, "rti_rbf_fit_soa: n = %d exceeds the supported %d nodes", n,
+                (4 * STG + TS * LDS) / 4 - 1);
     RTI_REQUIRE(smem <= 227 * 1024, "rti_rbf_fit_soa: n = %d needs %zu bytes of shared memory (> 227 KB)", n, smem);
     RTI_CUDA(cudaFuncSetAttribute(rbf_fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t grid = n_pixels < batch ? n_pixels : batch;
