@@ -196,31 +196,97 @@ rbf_fit_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const
                                 const int gr = kb * TS + r, gc = kb * TS + c;
                                 sD[r * SD_LD + c] = (gc >= M) ? ((gr == gc) ? 1.0 : 0.0) : acc[mi][ni][e];
                             }
-                    const int ur = t >> 2;                       // this thread updates row ur, columns uc0 + 4m
-                    const int uc0 = t & 3;
-                    for (int j = 0; j < TS; ++j) {
+                    // Blocked right-looking Cholesky, four 16-column panels.  Per panel: warp 0
+                    // factors the 16x16 diagonal block (warp barriers only), one thread per row
+                    // below it does the forward substitution of the panel, then all threads apply
+                    // the rank-16 update to the trailing lower triangle in 4x4 register tiles.
+                    // Columns >= cl are padding (identity) and are never touched.
+                    const int cl = min(TS, M - kb * TS);
+                    for (int jb = 0; jb < TS / 16; ++jb) {
+                        const int o = 16 * jb;
                         __syncthreads();
-                        const double piv = sD[j * SD_LD + j];
-                        const int gj = kb * TS + j;
-                        // relative pivot test against the original diagonal 2*a_j (duplicate nodes -> 0)
-                        const double ref = (gj < M) ? 2.0 * sa[gj + 1] : 1.0;
-                        if (!(piv > 1e-13 * ref) || !(piv > 0.0)) ok = false;
-                        const double rs = rsqrt(piv);
-                        if (t == 0) sRsq[j] = rs;
-                        const double ip = rs * rs;
-                        if (ur > j) {
-                            const double lrj = sD[ur * SD_LD + j] * ip;
-                            for (int c = uc0 + ((j + 1 - uc0 + 3) & ~3); c <= ur; c += 4)
-                                if (kb * TS + c < M)
-                                    sD[ur * SD_LD + c] = fma(-lrj, sD[c * SD_LD + j], sD[ur * SD_LD + c]);
+                        if (warp == 0) {
+                            for (int j = 0; j < 16; ++j) {
+                                const int cj = o + j;
+                                const double piv = sD[cj * SD_LD + cj];
+                                // relative pivot test against the original diagonal 2*a_j (duplicate nodes -> 0)
+                                const double ref = (cj < cl) ? 2.0 * sa[kb * TS + cj + 1] : 1.0;
+                                if (!(piv > 1e-13 * ref) || !(piv > 0.0)) ok = false;
+                                const double rs = rsqrt(piv);
+                                __syncwarp();
+                                const int r = cj + 1 + lane;
+                                if (lane == 0) { sD[cj * SD_LD + cj] = piv * rs; sRsq[cj] = rs; }
+                                if (r < o + 16) sD[r * SD_LD + cj] *= rs;
+                                __syncwarp();
+                                // trailing update inside the block: (r2, c) with cj < c <= r2 < o + 16
+                                const int r2 = cj + 1 + (lane >> 1);
+                                if (r2 < o + 16) {
+                                    const double lrj = sD[r2 * SD_LD + cj];
+                                    for (int c = cj + 1 + (lane & 1); c <= r2; c += 2)
+                                        if (c < cl)
+                                            sD[r2 * SD_LD + c] = fma(-lrj, sD[c * SD_LD + cj], sD[r2 * SD_LD + c]);
+                                }
+                                __syncwarp();
+                            }
+                        }
+                        if (jb == TS / 16 - 1) break;
+                        __syncthreads();
+                        // panel: X[r][o..o+15] = S[r][o..o+15] . L_jj^-T, one thread per row r >= o + 16
+                        if (t < TS - o - 16) {
+                            const int r = o + 16 + t;
+                            double x[16];
+#pragma unroll
+                            for (int c = 0; c < 16; ++c) x[c] = sD[r * SD_LD + o + c];
+#pragma unroll
+                            for (int pp = 0; pp < 16; ++pp) {
+                                if (o + pp < cl) {                          // padding columns keep their identity entries
+                                    x[pp] *= sRsq[o + pp];
+#pragma unroll
+                                    for (int c = pp + 1; c < 16; ++c)
+                                        if (o + c < cl) x[c] = fma(-x[pp], sD[(o + c) * SD_LD + o + pp], x[c]);
+                                }
+                            }
+#pragma unroll
+                            for (int c = 0; c < 16; ++c) sD[r * SD_LD + o + c] = x[c];
+                        }
+                        __syncthreads();
+                        // trailing update: S[r][c] -= sum_p X[r][p] X[c][p] for o + 16 <= c <= r < 64
+                        {
+                            const int tt = (TS - o - 16) / 4;                // micro tiles per side: 12, 8, 4
+                            const int tr = t / tt, tc = t - tr * tt;
+                            if (tr < tt && tc <= tr) {
+                                const int rb = o + 16 + 4 * tr, cb = o + 16 + 4 * tc;
+                                double u[4][4];
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                                    for (int j = 0; j < 4; ++j) u[i][j] = 0.0;
+#pragma unroll 4
+                                for (int pp = 0; pp < 16; ++pp) {
+                                    double xr[4], xc[4];
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i) {
+                                        xr[i] = sD[(rb + i) * SD_LD + o + pp];
+                                        xc[i] = sD[(cb + i) * SD_LD + o + pp];
+                                    }
+#pragma unroll
+                                    for (int i = 0; i < 4; ++i)
+#pragma unroll
+                                        for (int j = 0; j < 4; ++j) u[i][j] = fma(xr[i], xc[j], u[i][j]);
+                                }
+#pragma unroll
+                                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                                    for (int j = 0; j < 4; ++j)
+                                        if (cb + j <= rb + i && cb + j < cl) sD[(rb + i) * SD_LD + cb + j] -= u[i][j];
+                            }
                         }
                     }
                     __syncthreads();
-                    // scale columns: L[r][c] = S[r][c]/sqrt(piv_c); zero the strict upper triangle
+                    // zero the strict upper triangle (the staged tile was the full symmetric matrix)
                     for (int e = t; e < TS * TS; e += RBF_THREADS) {
                         const int r = e >> 6, c = e & 63;
-                        const double v = sD[r * SD_LD + c];
-                        sD[r * SD_LD + c] = (c < r) ? v * sRsq[c] : ((c == r) ? v * sRsq[c] : 0.0);
+                        if (c > r) sD[r * SD_LD + c] = 0.0;
                     }
                     __syncthreads();
                     // ---- Dinv by forward substitution, 4 threads per column k: sW[k][c] = Dinv[c][k]
