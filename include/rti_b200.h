@@ -149,6 +149,50 @@ int rti_rbf_grids(const float *d_lx, const float *d_ly, const double *d_weights,
                   int64_t n_pixels, int n, const double *d_axis, int g,
                   double *d_grids, rti_stream_t stream);
 
+/* ---- (3b) linear RBF, shared-light case ----------------------------------------------
+ * When every pixel sees the same n nodes (lx_i, ly_i) -- pixels_lx[y][x][:] identical for
+ * all (y, x) in the data handed to interpolate_intensities (analysis.py:341-343, 361) -- the
+ * per-pixel `Rbf(...)` + `rbf(xi, yi)` of analysis.py:259-260 is one matrix A for all
+ * pixels, so
+ *     grid values [g*g][P] = (Phi_grid . A^-1)[g*g][n] . D[n][P]      (RTI_RBF_OP_GRID)
+ *     weights     [n][P]   =  A^-1[n][n]               . D[n][P]      (RTI_RBF_OP_WEIGHTS)
+ * with D the intensities.  The operator is built once in fp64 by the per-pixel kernels run on
+ * n unit-intensity pseudo-pixels, each row scaled by a power of two and split into fp16
+ * hi + lo; the contraction runs on the tcgen05 tensor cores (TMA-fed, fp32 accumulation in
+ * TMEM; intensities are exact in fp16).
+ *
+ * d_op_hi / d_op_lo: fp16 bit patterns, rti_rbf_shared_operator_elems(op_rows, n) elements
+ * each ([op_rows rounded up to 128][n rounded up to 64], lights fastest), 16-byte aligned;
+ * d_inv_scale: float [op_rows] (op_rows = g*g or n).  d_bad counts singular systems
+ * (duplicate nodes; scipy: LinAlgError).
+ * d_packed: rti_rbf_shared_packed_elems(n, n_pixels) fp16 elements, 16-byte aligned: pixel
+ * blocks of 256, each a contiguous [n][256] slab (element (light i, pixel p) at
+ * ((p / 256) * n + i) * 256 + p % 256), produced by one of the two pack calls: from the uint8 frames
+ * (layout of rti_gather_soa's d_frames) or from int32 intensities [n_pixels][n]
+ * (compute_intensities layout; values outside [-2048, 2048] are not exact in fp16 and are
+ * counted in d_bad). */
+#define RTI_RBF_OP_GRID 0
+#define RTI_RBF_OP_WEIGHTS 1
+int64_t rti_rbf_shared_operator_elems(int op_rows, int n);
+int64_t rti_rbf_shared_packed_elems(int n, int64_t n_pixels);
+int rti_rbf_shared_operator(const float *d_lx, const float *d_ly, int n, const double *d_axis, int g,
+                            int kind, uint16_t *d_op_hi, uint16_t *d_op_lo, float *d_inv_scale,
+                            int32_t *d_bad, rti_stream_t stream);
+int rti_rbf_shared_pack_frames(const uint8_t *d_frames, int64_t frame_stride, int n, int64_t n_pixels,
+                               uint16_t *d_packed, rti_stream_t stream);
+int rti_rbf_shared_pack_soa(const int32_t *d_inten, int64_t n_pixels, int n, uint16_t *d_packed,
+                            int32_t *d_bad, rti_stream_t stream);
+/* prepare_images_data layout: d_table int32 [op_rows][image_stride] (op_rows = g*g), values
+ * truncated toward zero; d_bad counts threads that saw a value outside int32. */
+int rti_rbf_shared_table(const uint16_t *d_packed, int n, int64_t n_pixels, const uint16_t *d_op_hi,
+                         const uint16_t *d_op_lo, const float *d_inv_scale, int op_rows,
+                         int32_t *d_table, int64_t image_stride, int32_t *d_bad, rti_stream_t stream);
+/* pixel-major float64 [n_pixels][op_rows]: the layout of rti_rbf_grids (grid operator) or of
+ * rti_rbf_fit_soa's d_weights (weight operator). */
+int rti_rbf_shared_apply_f64(const uint16_t *d_packed, int n, int64_t n_pixels, const uint16_t *d_op_hi,
+                             const uint16_t *d_op_lo, const float *d_inv_scale, int op_rows,
+                             double *d_out, rti_stream_t stream);
+
 /* ---- relighting: relighting_event interactive_relighting.py:25-38 -----------------
  * Re-render one light direction (lu, lv) from the coefficient map: value =
  * trunc(poly(lu, lv)) clamped to [0, 255] (analysis.py:404-407 +

@@ -60,6 +60,13 @@ SIGNATURES = {
     "rti_rbf_fit_soa": (_i, [_p, _p, _p, _l, _i, _p, _p, _l, _i, _p, _p]),
     "rti_rbf_table": (_i, [_p, _p, _p, _l, _i, _p, _i, _p, _l, _p, _p]),
     "rti_rbf_grids": (_i, [_p, _p, _p, _l, _i, _p, _i, _p, _p]),
+    "rti_rbf_shared_operator_elems": (_l, [_i, _i]),
+    "rti_rbf_shared_packed_elems": (_l, [_i, _l]),
+    "rti_rbf_shared_operator": (_i, [_p, _p, _i, _p, _i, _i, _p, _p, _p, _p, _p]),
+    "rti_rbf_shared_pack_frames": (_i, [_p, _l, _i, _l, _p, _p]),
+    "rti_rbf_shared_pack_soa": (_i, [_p, _l, _i, _p, _p, _p]),
+    "rti_rbf_shared_table": (_i, [_p, _i, _l, _p, _p, _p, _i, _p, _l, _p, _p]),
+    "rti_rbf_shared_apply_f64": (_i, [_p, _i, _l, _p, _p, _p, _i, _p, _p]),
     "rti_relight_ptm": (_i, [_p, _l, _l, _d, _d, _p, _p, _p]),
     "rti_relight_ptm_f32": (_i, [_p, _l, _l, _f, _f, _p, _p, _p]),
     "rti_coef_to_f32": (_i, [_p, _l, _p, _p]),
