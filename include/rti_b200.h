@@ -90,6 +90,19 @@ int rti_ptm_fit_shared(const uint8_t *d_frames, int64_t frame_stride, const doub
                        int n, int64_t n_pixels,
                        double *d_coef, int64_t plane_stride, rti_stream_t stream);
 
+/* Shared-light detection: *d_flag is incremented when some pixel's (lx, ly) row differs
+ * (bitwise) from pixel 0's; it stays untouched when all n_pixels rows are identical, i.e.
+ * when the data handed to interpolate_intensities (analysis.py:341-343) has one light vector
+ * per frame for the whole ROI and the shared-light paths apply. */
+int rti_lights_shared(const float *d_lx, const float *d_ly, int64_t n_pixels, int n,
+                      int32_t *d_flag, rti_stream_t stream);
+/* The 6 x n pseudo-inverse of the common design matrix for rti_ptm_fit_shared, from the
+ * shared light components d_lx, d_ly (float32 [n]): pinv = (A^T A)^-1 A^T with A's rows
+ * (lu^2, lv^2, lu*lv, lu, lv, 1) formed like analysis.py:284-290; fp64.  d_bad is
+ * incremented when A is rank deficient. */
+int rti_ptm_shared_pinv(const float *d_lx, const float *d_ly, int n, double *d_pinv,
+                        int32_t *d_bad, rti_stream_t stream);
+
 /* ---- (4) light-grid evaluation ----------------------------------------------------
  * d_axis: float64 [g] grid axis values (analysis.py:345-347; the same axis is
  * used for lu and lv).  Value at (v, u): a0*lu^2 + a1*lv^2 + a2*lu*lv + a3*lu +

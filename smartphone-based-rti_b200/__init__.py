@@ -6,10 +6,11 @@ directory's name is not a Python identifier).
 from . import constants
 from ._capi import RtiError, RtiLibraryMissing, RtiSingularError
 from .analysis import (compute, compute_intensities, install, interpolate_intensities,
-                       light_axis, prepare_images_data, read_from_file, write_on_file)
+                       interpolate_shared_light, light_axis, prepare_images_data, read_from_file,
+                       write_on_file)
 
 __all__ = [
     "constants", "compute", "compute_intensities", "interpolate_intensities", "prepare_images_data",
-    "install", "light_axis", "read_from_file", "write_on_file", "RtiError", "RtiLibraryMissing",
+    "install", "interpolate_shared_light", "light_axis", "read_from_file", "write_on_file", "RtiError", "RtiLibraryMissing",
     "RtiSingularError",
 ]

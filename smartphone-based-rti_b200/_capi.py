@@ -52,6 +52,8 @@ SIGNATURES = {
     "rti_ptm_fit_frames": (_i, [_p, _l, _p, _i, _i, _i, _i, _p, _l, _p, _p]),
     "rti_ptm_fit_soa": (_i, [_p, _p, _p, _l, _i, _p, _l, _p, _p]),
     "rti_ptm_fit_shared": (_i, [_p, _l, _p, _i, _l, _p, _l, _p]),
+    "rti_lights_shared": (_i, [_p, _p, _l, _i, _p, _p]),
+    "rti_ptm_shared_pinv": (_i, [_p, _p, _i, _p, _p, _p]),
     "rti_ptm_table": (_i, [_p, _l, _l, _p, _i, _p, _l, _p, _p]),
     "rti_ptm_grids": (_i, [_p, _l, _l, _p, _i, _p, _p]),
     "rti_ptm_fit_table_frames": (_i, [_p, _l, _p, _i, _i, _i, _i, _p, _i, _p, _l, _p, _l, _p, _p]),

@@ -163,10 +163,11 @@ class InterpolationResult:
     PTM: coefficient map float64 (6, P);  RBF: nodes (lx, ly) and weights float64 (P, N).
     A pixel's grid is evaluated on demand."""
 
-    def __init__(self, mode, rows, cols, axis, coef=None, lx=None, ly=None, weights=None, row0=0):
+    def __init__(self, mode, rows, cols, axis, coef=None, lx=None, ly=None, weights=None, row0=0, shared=None):
         self.mode, self.rows, self.cols, self.row0 = mode, rows, cols, row0
         self.axis = np.ascontiguousarray(axis, dtype=np.float64)
         self.coef, self.lx, self.ly, self.weights = coef, lx, ly, weights
+        self.shared = shared            # mode "rbf_shared": a SharedLightRbf
         self._d_axis = None
 
     @property
@@ -194,6 +195,8 @@ class InterpolationResult:
         if self.mode == "ptm":
             _capi.call("rti_ptm_grids", self.coef.data_ptr() + 8 * p0, self.n_pixels, count,
                        self.d_axis().data_ptr(), g, out.data_ptr(), _stream_ptr(torch))
+        elif self.mode == "rbf_shared":
+            out = self.shared.grids(p0, count).view(count, g, g)
         else:
             n = self.weights.shape[1]
             _capi.call("rti_rbf_grids", self.lx.data_ptr() + 4 * p0 * n, self.ly.data_ptr() + 4 * p0 * n,
@@ -255,6 +258,139 @@ def _as_device_soa(data, range_val):
     return tuple(out)
 
 
+class SharedLightRbf:
+    """Linear RBF when every pixel has the same n nodes: one operator for all pixels
+    (rti_rbf_shared_operator) applied to the packed intensities on the tensor cores."""
+
+    def __init__(self, lx1, ly1, axis, d_axis):
+        torch = _torch()
+        self.lib = _capi.load()
+        self.lx1, self.ly1 = lx1.contiguous(), ly1.contiguous()          # float32 (n,) on the device
+        self.n = int(lx1.numel())
+        self.g = int(axis.size)
+        self.d_axis = d_axis
+        self._ops = {}
+        self.packed, self.n_pixels = None, 0
+        self.bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+
+    def operator(self, kind):
+        """(hi, lo, inv_scale, rows) of the grid (kind 0) or weight (kind 1) operator."""
+        if kind not in self._ops:
+            torch = _torch()
+            rows = self.g * self.g if kind == 0 else self.n
+            elems = self.lib.rti_rbf_shared_operator_elems(rows, self.n)
+            hi = torch.empty(elems, dtype=torch.int16, device="cuda")
+            lo = torch.empty(elems, dtype=torch.int16, device="cuda")
+            inv = torch.empty(rows, dtype=torch.float32, device="cuda")
+            _capi.call("rti_rbf_shared_operator", self.lx1.data_ptr(), self.ly1.data_ptr(), self.n,
+                       self.d_axis.data_ptr(), self.g, kind, hi.data_ptr(), lo.data_ptr(), inv.data_ptr(),
+                       self.bad.data_ptr(), _stream_ptr(torch))
+            _raise_if_bad(self.bad, "RBF")
+            self._ops[kind] = (hi, lo, inv, rows)
+        return self._ops[kind]
+
+    def _new_packed(self, n_pixels):
+        torch = _torch()
+        return torch.empty(self.lib.rti_rbf_shared_packed_elems(self.n, n_pixels), dtype=torch.int16, device="cuda")
+
+    def pack_frames(self, d_frames, n_pixels):
+        """uint8 frames (n, n_pixels) on the device -> packed fp16 intensities."""
+        self.packed, self.n_pixels = self._new_packed(n_pixels), n_pixels
+        _capi.call("rti_rbf_shared_pack_frames", d_frames.data_ptr(), n_pixels, self.n, n_pixels,
+                   self.packed.data_ptr(), _stream_ptr(_torch()))
+
+    def pack_soa(self, inten):
+        """int32 intensities (n_pixels, n) on the device -> packed fp16; False if not exact in fp16."""
+        torch = _torch()
+        n_pixels = int(inten.shape[0])
+        packed = self._new_packed(n_pixels)
+        flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        _capi.call("rti_rbf_shared_pack_soa", inten.data_ptr(), n_pixels, self.n, packed.data_ptr(),
+                   flag.data_ptr(), _stream_ptr(torch))
+        if int(flag.item()) > 0:
+            return False
+        self.packed, self.n_pixels = packed, n_pixels
+        return True
+
+    def _block(self, p0, count):
+        """Packed sub-range: whole 256-pixel blocks only (the packed layout is blocked)."""
+        if p0 % 256 != 0:
+            raise ValueError("shared-light sub-ranges start on a 256-pixel block")
+        return self.packed.data_ptr() + 2 * p0 * self.n
+
+    def table(self, out, image_stride, bad):
+        hi, lo, inv, rows = self.operator(0)
+        _capi.call("rti_rbf_shared_table", self.packed.data_ptr(), self.n, self.n_pixels, hi.data_ptr(),
+                   lo.data_ptr(), inv.data_ptr(), rows, out.data_ptr(), image_stride, bad.data_ptr(),
+                   _stream_ptr(_torch()))
+
+    def _apply(self, kind, p0, count):
+        torch = _torch()
+        hi, lo, inv, rows = self.operator(kind)
+        b0 = (p0 // 256) * 256
+        cnt = min(self.n_pixels, p0 + count) - b0
+        out = torch.empty((cnt, rows), dtype=torch.float64, device="cuda")
+        _capi.call("rti_rbf_shared_apply_f64", self._block(b0, cnt), self.n, cnt, hi.data_ptr(), lo.data_ptr(),
+                   inv.data_ptr(), rows, out.data_ptr(), _stream_ptr(torch))
+        return out[p0 - b0:p0 - b0 + count]
+
+    def grids(self, p0, count):
+        """float64 (count, g*g) grid values of pixels [p0, p0 + count)."""
+        return self._apply(0, p0, count)
+
+    def weights(self, p0=0, count=None):
+        """float64 (count, n) RBF weights (scipy Rbf.nodes) of pixels [p0, p0 + count)."""
+        return self._apply(1, p0, self.n_pixels - p0 if count is None else count)
+
+
+def lights_are_shared(lx, ly):
+    """True when every pixel row of the device tensors lx, ly (P, n) equals pixel 0's."""
+    torch = _torch()
+    n_pixels, n = lx.shape
+    if n_pixels < 2:
+        return False                       # a single pixel: nothing to share
+    # cheap rejection first: the per-pixel data of compute_intensities differs at once
+    if not (torch.equal(lx[0], lx[n_pixels - 1]) and torch.equal(ly[0], ly[n_pixels - 1])):
+        return False
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_lights_shared", lx.data_ptr(), ly.data_ptr(), n_pixels, n, flag.data_ptr(), _stream_ptr(torch))
+    return int(flag.item()) == 0
+
+
+def interpolate_shared_light(data, lx, ly, interpolate_PTM=False):
+    """Shared-light entry: frame records as for compute_intensities plus ONE light vector per
+    frame (lx[i], ly[i]) valid for the whole ROI (distant light).  Same result object as
+    interpolate_intensities would give for pixels_lx[y][x][:] = lx, pixels_ly[y][x][:] = ly,
+    without materialising the (R, R, N) arrays: PTM is coef = pinv . I (rti_ptm_fit_shared),
+    linear RBF one tensor-core contraction (rti_rbf_shared_*)."""
+    if data is None or len(data) <= 0:
+        raise Exception("Error computing interpolation: results are empty or invalid")
+    torch = _torch()
+    range_val = _cst.ROI_DIAMETER
+    stack = data if isinstance(data, FrameStack) else FrameStack(*_stack_frames(data, range_val, range_val))
+    lx1 = torch.from_numpy(np.ascontiguousarray(lx, dtype=np.float32).reshape(-1)).cuda()
+    ly1 = torch.from_numpy(np.ascontiguousarray(ly, dtype=np.float32).reshape(-1)).cuda()
+    if lx1.numel() != stack.n or ly1.numel() != stack.n:
+        raise ValueError("need one (lx, ly) per frame: %d frames, %d / %d values" % (stack.n, lx1.numel(), ly1.numel()))
+    axis = light_axis()
+    p = stack.n_pixels
+    if interpolate_PTM:
+        pinv = torch.empty((6, stack.n), dtype=torch.float64, device="cuda")
+        bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+        _capi.call("rti_ptm_shared_pinv", lx1.data_ptr(), ly1.data_ptr(), stack.n, pinv.data_ptr(), bad.data_ptr(),
+                   _stream_ptr(torch))
+        _raise_if_bad(bad, "PTM")
+        coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+        _capi.call("rti_ptm_fit_shared", stack.d_frames.data_ptr(), p, pinv.data_ptr(), stack.n, p,
+                   coef.data_ptr(), p, _stream_ptr(torch))
+        return InterpolationResult("ptm", stack.rows, stack.cols, axis, coef=coef, row0=stack.row0)
+    res = InterpolationResult("rbf_shared", stack.rows, stack.cols, axis, row0=stack.row0)
+    res.shared = SharedLightRbf(lx1, ly1, axis, res.d_axis())
+    res.shared.pack_frames(stack.d_frames, p)
+    res.shared.operator(0)                 # raises RtiSingularError on duplicate nodes, like scipy's LinAlgError
+    return res
+
+
 def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
     """Interpolate pixel intensities (analysis.py:321-372).
 
@@ -289,6 +425,13 @@ def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
                    coef.data_ptr(), n_pixels, bad.data_ptr(), _stream_ptr(torch))
         _raise_if_bad(bad, "PTM")
         return InterpolationResult("ptm", range_val, range_val, axis, coef=coef)
+    if lights_are_shared(lx, ly):
+        # one light vector per frame for the whole ROI: one operator, one tensor-core contraction
+        res = InterpolationResult("rbf_shared", range_val, range_val, axis)
+        res.shared = SharedLightRbf(lx[0].clone(), ly[0].clone(), axis, res.d_axis())
+        if res.shared.pack_soa(inten):     # intensities exact in fp16 (always true for uint8 frames)
+            res.shared.operator(0)
+            return res
     weights = rbf_fit_device(lx, ly, inten, bad)
     _raise_if_bad(bad, "RBF")
     return InterpolationResult("rbf", range_val, range_val, axis, lx=lx, ly=ly, weights=weights)
@@ -329,6 +472,8 @@ def table_device(res: InterpolationResult, out=None):
     if res.mode == "ptm":
         _capi.call("rti_ptm_table", res.coef.data_ptr(), p, p, res.d_axis().data_ptr(), g,
                    out.data_ptr(), p, bad.data_ptr(), _stream_ptr(torch))
+    elif res.mode == "rbf_shared":
+        res.shared.table(out, p, bad)
     else:
         n = res.weights.shape[1]
         _capi.call("rti_rbf_table", res.lx.data_ptr(), res.ly.data_ptr(), res.weights.data_ptr(), p, n,

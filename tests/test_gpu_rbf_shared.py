@@ -219,3 +219,68 @@ def test_shared_equals_per_pixel_kernels(torch_cuda):
     torch.cuda.synchronize()
     vals = grids.cpu().numpy().reshape(p, g * g).T
     check_table(table, vals, GRID_RTOL_ACHIEVED * np.max(np.abs(vals)))
+
+
+# ------------------------------------------------------------------ host call surface
+def test_call_surface_detects_shared_lights(torch_cuda, monkeypatch):
+    """interpolate_intensities(data) with pixels_lx[y][x][:] identical for all pixels takes the
+    shared-light contraction and returns what the per-pixel algorithm returns."""
+    import rti_b200
+    r, n = 20, 60
+    monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", r)
+    monkeypatch.setattr(rti_b200.constants, "INTERPOLATION_PARAM", 0.1)
+    lx1, ly1 = shared_nodes(n, seed=21)
+    rng = np.random.default_rng(6)
+    inten = rng.integers(0, 256, (r, r, n)).astype(np.int32)
+    lx = np.ascontiguousarray(np.broadcast_to(lx1, (r, r, n)))
+    ly = np.ascontiguousarray(np.broadcast_to(ly1, (r, r, n)))
+    res = rti_b200.interpolate_intensities((lx, ly, inten))
+    assert res.mode == "rbf_shared"
+    axis = orc.light_axis(0.1)
+    frames = np.ascontiguousarray(inten.reshape(r * r, n).T).astype(np.uint8)
+    w_ref, vals = oracle_shared(lx1, ly1, frames, axis)
+    scale = np.max(np.abs(vals))
+    for (y, x) in [(0, 0), (3, 17), (19, 19), (12, 16)]:           # pixel 272 = (13, 12) is in the 2nd block
+        ref = vals[:, y * r + x].reshape(axis.size, axis.size)
+        assert np.max(np.abs(res[y][x] - ref)) <= GRID_RTOL_ACHIEVED * scale
+    table = np.array(rti_b200.prepare_images_data(res)).reshape(axis.size ** 2, r * r)
+    check_table(table, vals, GRID_RTOL_ACHIEVED * scale)
+    w = res.shared.weights().cpu().numpy()
+    assert np.max(np.abs(w.T - w_ref)) <= 1e-4 * np.max(np.abs(w_ref))
+    # per-pixel data is not mistaken for shared data
+    lx[7, 3, 11] = np.nextafter(lx[7, 3, 11], np.float32(1))
+    assert rti_b200.interpolate_intensities((lx, ly, inten)).mode == "rbf"
+
+
+def test_interpolate_shared_light_entry(torch_cuda, monkeypatch):
+    """frame records + one light vector per frame: PTM (pinv contraction) and RBF (tcgen05)."""
+    import rti_b200
+    from rti_b200 import synthetic
+    r, n = 24, 45
+    monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", r)
+    monkeypatch.setattr(rti_b200.constants, "INTERPOLATION_PARAM", 0.25)
+    lx1, ly1 = shared_nodes(n, seed=33)
+    rng = np.random.default_rng(9)
+    frames = rng.integers(0, 256, (n, r, r), dtype=np.uint8)
+    cams = rng.uniform(0, 1, (n, 3))
+    records = synthetic.as_records(frames, cams)
+    inten = np.transpose(frames, (1, 2, 0)).astype(np.int32)
+    lx = np.broadcast_to(lx1, (r, r, n))
+    ly = np.broadcast_to(ly1, (r, r, n))
+    # PTM
+    res = rti_b200.interpolate_shared_light(records, lx1, ly1, interpolate_PTM=True)
+    ref = orc.ptm_fit_batch(lx, ly, inten)
+    coef = res.coefficients().transpose(1, 2, 0)
+    assert np.max(np.abs(coef - ref) / np.max(np.abs(ref), axis=2, keepdims=True)) < 1e-9
+    # RBF
+    res = rti_b200.interpolate_shared_light(records, lx1, ly1)
+    axis = orc.light_axis(0.25)
+    _, vals = oracle_shared(lx1, ly1, frames.reshape(n, r * r), axis)
+    table = np.array(rti_b200.prepare_images_data(res)).reshape(axis.size ** 2, r * r)
+    check_table(table, vals, GRID_RTOL_ACHIEVED * np.max(np.abs(vals)))
+    # duplicate nodes: scipy raises LinAlgError, we raise RtiSingularError
+    lx1[4], ly1[4] = lx1[9], ly1[9]
+    with pytest.raises(rti_b200.RtiSingularError):
+        rti_b200.interpolate_shared_light(records, lx1, ly1)
+    with pytest.raises(ValueError):
+        rti_b200.interpolate_shared_light(records, lx1[:5], ly1[:5])
