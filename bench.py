@@ -161,6 +161,94 @@ def run_reference(args, rank):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------- linear-RBF side measurements
+def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
+    """The two linear-RBF forms of the same workload on bounded pixel samples (not part of `value`):
+    per-pixel lights (the reference's semantics: fp64 DMMA Cholesky + fp64 grid evaluation) on 2 ROI
+    rows, and shared lights (one tcgen05 contraction) on 256 ROI rows.  Device-timed, best of 3."""
+    S = torch.cuda.current_stream().cuda_stream
+
+    def best(fn, reps=3):
+        fn()
+        torch.cuda.synchronize()
+        out = []
+        for _ in range(reps):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            out.append(a.elapsed_time(b))
+        return min(out)
+
+    res = {}
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    # ---- per-pixel lights: rows [0, 2) of the slab
+    px = 2 * COLS
+    lx = torch.empty((px, N_LIGHTS), dtype=torch.float32, device="cuda")
+    ly = torch.empty_like(lx)
+    inten = torch.empty((px, N_LIGHTS), dtype=torch.int32, device="cuda")
+    _capi.call("rti_gather_soa", d_frames.data_ptr(), p, d_cams.data_ptr(), N_LIGHTS, 0, 2, COLS,
+               lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), S)
+    w = torch.empty((px, N_LIGHTS), dtype=torch.float64, device="cuda")
+    batch = 148 * 2
+    nbytes = lib.rti_rbf_workspace_bytes(N_LIGHTS, batch)
+    work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    tab = torch.empty((G, G, px), dtype=torch.int32, device="cuda")
+    fit_ms = best(lambda: _capi.call("rti_rbf_fit_soa", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), px, N_LIGHTS,
+                                     w.data_ptr(), work.data_ptr(), nbytes, batch, bad.data_ptr(), S))
+    ev_ms = best(lambda: _capi.call("rti_rbf_table", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), px, N_LIGHTS,
+                                    d_axis.data_ptr(), G, tab.data_ptr(), px, bad.data_ptr(), S))
+    res["rbf_per_pixel_lights"] = {
+        "sample": "%d pixels (2 ROI rows) x %d lights, fit + 100x100 table" % (px, N_LIGHTS),
+        "fit_ms": fit_ms, "table_ms": ev_ms, "value": px * N_LIGHTS / ((fit_ms + ev_ms) * 1e-3) / 1e6, "unit": UNIT,
+        "fit_fp64_tflops": (N_LIGHTS ** 3 / 3.0) * 2 * px / (fit_ms * 1e-3) / 1e12,
+        "bound": "fp64 tensor pipe (fit), fp64 pipe (evaluation)", "singular": int(bad.item())}
+    del lx, ly, inten, w, work, tab
+    # ---- shared lights: rows [0, 256) of the slab, nodes = the light vectors seen from the ROI centre
+    rows = 256
+    px = rows * COLS
+    cams = d_cams.cpu().numpy()
+    c = np.array([COLS / 2.0, ROWS / 2.0, 0.0])
+    l = (cams - c) / np.linalg.norm(cams - c, axis=1, keepdims=True)
+    d_lx = torch.from_numpy(l[:, 0].astype(np.float32)).cuda()
+    d_ly = torch.from_numpy(l[:, 1].astype(np.float32)).cuda()
+    op_rows = G * G
+    elems = lib.rti_rbf_shared_operator_elems(op_rows, N_LIGHTS)
+    hi = torch.empty(elems, dtype=torch.int16, device="cuda")
+    lo = torch.empty(elems, dtype=torch.int16, device="cuda")
+    inv = torch.empty(op_rows, dtype=torch.float32, device="cuda")
+    packed = torch.empty(lib.rti_rbf_shared_packed_elems(N_LIGHTS, px), dtype=torch.int16, device="cuda")
+    tab = torch.empty((op_rows, px), dtype=torch.int32, device="cuda")
+    bad.zero_()
+    op_ms = best(lambda: _capi.call("rti_rbf_shared_operator", d_lx.data_ptr(), d_ly.data_ptr(), N_LIGHTS,
+                                    d_axis.data_ptr(), G, 0, hi.data_ptr(), lo.data_ptr(), inv.data_ptr(),
+                                    bad.data_ptr(), S), reps=1)
+    pack_ms = best(lambda: _capi.call("rti_rbf_shared_pack_frames", d_frames.data_ptr(), p, N_LIGHTS, px,
+                                      packed.data_ptr(), S))
+    gemm_ms = best(lambda: _capi.call("rti_rbf_shared_table", packed.data_ptr(), N_LIGHTS, px, hi.data_ptr(),
+                                      lo.data_ptr(), inv.data_ptr(), op_rows, tab.data_ptr(), px, bad.data_ptr(), S))
+    n_pad, r_pad = -(-N_LIGHTS // 64) * 64, -(-op_rows // 128) * 128
+    executed = 4.0 * r_pad * n_pad * px / (gemm_ms * 1e-3) / 1e12
+    tensor_peak = None
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            tensor_peak = float(json.load(f)["bf16_tflops"])
+    except Exception:
+        pass
+    res["rbf_shared_lights"] = {
+        "sample": "%d pixels (%d ROI rows) x %d lights, pack + tcgen05 contraction into the 100x100 table"
+                  % (px, rows, N_LIGHTS),
+        "operator_build_ms": op_ms, "pack_ms": pack_ms, "contraction_ms": gemm_ms,
+        "value": px * N_LIGHTS / ((pack_ms + gemm_ms) * 1e-3) / 1e6, "unit": UNIT,
+        "roofline": {"bound": "tensor", "achieved": executed, "peak": tensor_peak, "unit": "TFLOP/s",
+                     "frac": (executed / tensor_peak) if tensor_peak else None,
+                     "note": "executed fp16 flops: hi + lo operator halves on the padded shape; peak = measured "
+                             "burst bf16 (MEASURED_PEAKS.json bf16_tflops)"},
+        "singular": int(bad.item())}
+    return res
+
+
 # ------------------------------------------------------------------------------ GPU arm
 def run_gpu(args, rank, local_rank, world):
     import torch
@@ -298,6 +386,10 @@ def run_gpu(args, rank, local_rank, world):
                    "api": "rti_ptm_compute_host (pinned host frames -> int32 table in pinned host memory)"}
             lib.rti_destroy()
 
+    secondary = None
+    if world == 1 and not args.no_secondary:
+        secondary = secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p)
+
     if rank != 0:
         return
 
@@ -326,6 +418,7 @@ def run_gpu(args, rank, local_rank, world):
                    "l2": "inputs (524 MB) and the 42 GB table written per step exceed the 126 MB L2"},
         "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "kernel_ms": {"ptm_fused": fused_ms, "ptm_fit_frames": fit_ms, "ptm_table": table_ms},
+        "secondary": secondary,
     }
     print(json.dumps(line), flush=True)
 
@@ -339,6 +432,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the linear-RBF side measurements")
     ap.add_argument("--cpu-pixels-per-core", type=int, default=96)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup
