@@ -79,7 +79,9 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
 // LDS.128 reads (row = thread) are both bank-conflict free.  Every thread then owns its
 // pixel's 26 running sums: no cross-lane reduction, and the 6x6 solves run on all lanes.
 // Lights past n and pixels past n_pixels are zero-filled by cp.async (src-size 0), which
-// adds exact zeros to the sums.
+// adds exact zeros to the sums.  The 16-byte chunks are aligned in memory for ANY n: when
+// n % 4 != 0 a row's first chunk starts with 1-3 elements of the previous row, which the
+// owning thread zeroes after the load.
 // Bound: 12 B of HBM per pixel.light against 32 fp64 issue slots + 6 conversions; at full
 // fp64 rate that is ~7 TB/s, i.e. the kernel sits at the HBM / fp64 ridge.
 // --------------------------------------------------------------------------------------
@@ -117,12 +119,16 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
                 const int rem = idx - a * (SOA_PIX * 8);
                 const int row = rem >> 3, c = rem & 7;
                 const int64_t p = p0 + row;
-                const int light = i0 + 4 * c;
-                int nb = (p < n_pixels) ? (n - light) * 4 : 0;
+                // 16-byte chunks are aligned in MEMORY, not in the light index: a row starts at element
+                // p*n, which is a multiple of 4 only when n is.  The chunk holding the row start may
+                // begin with up to 3 elements of the previous row; the consumer masks them.
+                const int64_t e0 = p * n;
+                const int64_t start = (e0 & ~(int64_t)3) + i0 + 4 * c;
+                int64_t nb = (p < n_pixels) ? (e0 + n - start) * 4 : 0;
                 nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
                 const char *src = reinterpret_cast<const char *>(base[a]);
-                if (nb > 0) src += (p * n + light) * 4;
-                cp_async_zfill(dst0 + a * SOA_ARRAY_BYTES + row * 128 + ((c ^ (row & 7)) << 4), src, 16, nb);
+                if (nb > 0) src += start * 4;
+                cp_async_zfill(dst0 + a * SOA_ARRAY_BYTES + row * 128 + ((c ^ (row & 7)) << 4), src, 16, (int)nb);
             }
         } else {
             for (int it = 0; it < 3 * SOA_KL; ++it) {
@@ -144,7 +150,9 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
 
     NormalEq ne;
     ne.clear();
-    const int n_stages = (n + SOA_KL - 1) / SOA_KL;
+    // VEC16 with n % 4 != 0: rows are misaligned by up to 3 elements, one more stage may be needed
+    const int n_stages = (n + ((VEC16 && (n & 3)) ? 3 : 0) + SOA_KL - 1) / SOA_KL;
+    const int lead = VEC16 ? (int)(((p0 + t) * n) & 3) : 0;         // elements of the previous row in chunk 0
     issue(0, 0);
     for (int s = 0; s < n_stages; ++s) {
         if (s + 1 < n_stages) {
@@ -158,9 +166,14 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
 #pragma unroll 2
         for (int c = 0; c < 8; ++c) {
             const int off = (c ^ (t & 7)) << 4;
-            const float4 u = *reinterpret_cast<const float4 *>(row + off);
-            const float4 v = *reinterpret_cast<const float4 *>(row + SOA_ARRAY_BYTES + off);
-            const int4 w = *reinterpret_cast<const int4 *>(row + 2 * SOA_ARRAY_BYTES + off);
+            float4 u = *reinterpret_cast<const float4 *>(row + off);
+            float4 v = *reinterpret_cast<const float4 *>(row + SOA_ARRAY_BYTES + off);
+            int4 w = *reinterpret_cast<const int4 *>(row + 2 * SOA_ARRAY_BYTES + off);
+            if (VEC16 && s == 0 && c == 0 && lead > 0) {               // zero = no contribution (see above)
+                u.x = v.x = 0.0f, w.x = 0;
+                if (lead > 1) u.y = v.y = 0.0f, w.y = 0;
+                if (lead > 2) u.z = v.z = 0.0f, w.z = 0;
+            }
             ne.add(u.x, v.x, (double)w.x);
             ne.add(u.y, v.y, (double)w.y);
             ne.add(u.z, v.z, (double)w.z);
@@ -267,7 +280,7 @@ extern "C" int rti_ptm_fit_soa(const float *d_lx, const float *d_ly, const int32
     RTI_REQUIRE(plane_stride >= n_pixels, "rti_ptm_fit_soa: plane_stride < pixels");
     const int64_t blocks = (n_pixels + SOA_PIX - 1) / SOA_PIX;
     RTI_REQUIRE(blocks <= 0x7fffffffLL, "rti_ptm_fit_soa: too many pixels");
-    const bool vec16 = (n % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_lx) & 15) == 0) &&
+    const bool vec16 = ((reinterpret_cast<uintptr_t>(d_lx) & 15) == 0) &&
                        ((reinterpret_cast<uintptr_t>(d_ly) & 15) == 0) &&
                        ((reinterpret_cast<uintptr_t>(d_inten) & 15) == 0);
     RTI_CUDA(cudaFuncSetAttribute(ptm_fit_soa_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOA_SMEM));

@@ -83,7 +83,12 @@ def test_gather_matches_reference_golden(torch_cuda, ref_small):
 
 
 @pytest.mark.parametrize("rows,cols,n,row0", [(1, 1, 1, 0), (3, 5, 7, 0), (9, 33, 130, 4), (16, 64, 256, 0),
-                                              (5, 40, 129, 11), (2, 31, 4, 0)])
+                                              (5, 40, 129, 11), (2, 31, 4, 0),
+                                              # n % 8 == 0: the TMA-store kernel (64-frame chunks, 32-pixel CTAs); n % 8 == 4: 16-byte stores
+                                              (5, 37, 132, 3), (2, 50, 64, 0), (7, 31, 200, 1), (1, 33, 68, 0),
+                                              (3, 100, 500, 2), (4, 45, 136, 1), (2, 70, 504, 0),
+                                              # n % 4 != 0 with several 128-frame chunks: coalesced scalar stores
+                                              (2, 41, 301, 0), (3, 35, 259, 5)])
 def test_gather_ragged_shapes(torch_cuda, rows, cols, n, row0):
     from rti_b200 import synthetic
     frames, cams = synthetic.random_stack(rows, cols, n, seed=rows * 100 + n, rows_total=rows + row0)
@@ -127,10 +132,12 @@ def test_ptm_fit_frames_shapes(torch_cuda, rows, cols, n, row0):
     assert coef_rel_err(coef.cpu().numpy().T, ref) < tol
 
 
-def test_ptm_fit_soa_matches_frames_path(torch_cuda):
+@pytest.mark.parametrize("rows,cols,n", [(6, 21, 203), (5, 27, 64), (3, 50, 33), (9, 17, 130), (2, 129, 97),
+                                         (4, 33, 6), (7, 19, 31)])
+def test_ptm_fit_soa_matches_frames_path(torch_cuda, rows, cols, n):
+    """Every residue of n mod 4: the 16-byte staging is aligned in memory, not in the light index."""
     from rti_b200 import _capi, synthetic
     torch = torch_cuda
-    rows, cols, n = 6, 21, 203
     frames, cams = synthetic.lambertian_stack(rows, cols, n, seed=8)
     lx, ly, inten = orc.gather_soa(frames, cams)
     p = rows * cols
@@ -141,9 +148,10 @@ def test_ptm_fit_soa_matches_frames_path(torch_cuda):
     torch.cuda.synchronize()
     assert int(bad.item()) == 0
     ref = orc.ptm_fit_batch(lx, ly, inten).reshape(-1, 6)
-    assert coef_rel_err(coef.cpu().numpy().T, ref) < PTM_COEF_RTOL
+    tol = 1e-7 if n == 6 else PTM_COEF_RTOL                            # N = 6 is exactly determined
+    assert coef_rel_err(coef.cpu().numpy().T, ref) < tol
     fused, _ = gpu_fit_frames(torch, frames, cams)
-    assert coef_rel_err(coef.cpu().numpy().T, fused.cpu().numpy().T) < 1e-11
+    assert coef_rel_err(coef.cpu().numpy().T, fused.cpu().numpy().T) < (1e-7 if n == 6 else 1e-11)
 
 
 def test_ptm_analytic_kat(torch_cuda):
