@@ -26,7 +26,7 @@ import sys
 
 import numpy as np
 
-from . import _capi
+from . import _capi, table_io
 from . import constants as _default_constants
 
 _cst = _default_constants           # rebound by install() to the reference's constants module
@@ -534,8 +534,12 @@ def write_on_file(data, filename, compressed=True):
             pickle.dump(data, f)
     else:
         filename = filename + ".pickle"
+        slab = table_io.is_table_slab(data)          # the nested list of views prepare_images_data returns
         with open(filename, "wb") as f:
-            pickle.dump(data, f)
+            if slab is not None and slab.nbytes > 0:
+                table_io.dump_table(slab, f)         # same object graph, no per-image copies
+            else:
+                pickle.dump(data, f)
     print("Saved file {}".format(filename))
 
 
@@ -587,7 +591,7 @@ def compute(video_name="coin1", from_storage=False, storage_filepath=None, inter
     return results_images
 
 
-def install(analysis_module, constants_module=None):
+def install(analysis_module, constants_module=None, fast_writer=True):
     """Drop-in: rebind the reference module's hot functions to this implementation.
 
     analysis.compute() resolves compute_intensities / interpolate_intensities /
@@ -603,4 +607,19 @@ def install(analysis_module, constants_module=None):
     analysis_module.compute_intensities = compute_intensities
     analysis_module.interpolate_intensities = interpolate_intensities
     analysis_module.prepare_images_data = prepare_images_data
+    # analysis.compute() stores the table with ut.write_on_file(.., compressed=False) (analysis.py:475):
+    # route that one call shape through the streaming writer; everything else goes to the original
+    ut = getattr(analysis_module, "ut", None)
+    if fast_writer and ut is not None and hasattr(ut, "write_on_file") \
+            and not getattr(ut.write_on_file, "_rti_b200", False):
+        original = ut.write_on_file
+
+        def write_on_file_fast(data, filename, compressed=True):
+            if compressed or table_io.is_table_slab(data) is None:
+                return original(data, filename, compressed=compressed)
+            return write_on_file(data, filename, compressed=False)
+
+        write_on_file_fast._rti_b200 = True
+        write_on_file_fast._original = original
+        ut.write_on_file = write_on_file_fast
     return analysis_module

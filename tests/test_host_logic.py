@@ -109,3 +109,54 @@ def test_install_rebinds_reference_module():
         assert analysis.light_axis().size == 4               # now reads the reference's constants
     finally:
         analysis._cst = old
+
+
+# ------------------------------------------------------------------ streaming table writer (8(f1))
+def test_dump_table_round_trips_like_pickle_dump(tmp_path):
+    import pickle
+    from rti_b200 import table_io
+    rng = np.random.default_rng(0)
+    table = rng.integers(-500, 500, (5, 7, 6, 6)).astype(np.int32)
+    images = [[table[v, u] for u in range(7)] for v in range(5)]
+    assert table_io.is_table_slab(images) is table
+    out = pickle.loads(table_io.dumps_table(table))
+    ref = pickle.loads(pickle.dumps(images))
+    assert type(out) is list and len(out) == 5 and all(type(r) is list and len(r) == 7 for r in out)
+    for v in range(5):
+        for u in range(7):
+            a = out[v][u]
+            assert a.dtype == np.int32 and a.shape == (6, 6) and a.flags.writeable and a.flags.c_contiguous
+            assert np.array_equal(a, ref[v][u])
+    # interactive_relighting.py:35-36 clamps the looked-up image in place
+    out[2][3][out[2][3] > 255] = 255
+    out[2][3][out[2][3] <= 0] = 0
+    assert out[2][3].min() >= 0 and out[2][3].max() <= 255
+
+
+def test_is_table_slab_rejects_anything_else():
+    from rti_b200 import table_io
+    table = np.zeros((3, 4, 2, 2), np.int32)
+    assert table_io.is_table_slab([[table[v, u].copy() for u in range(4)] for v in range(3)]) is None
+    assert table_io.is_table_slab([[table[v, u] for u in range(3)] for v in range(3)]) is None       # ragged vs base
+    assert table_io.is_table_slab([[table[u % 3, v] for u in range(4)] for v in range(3)]) is None   # permuted
+    assert table_io.is_table_slab([]) is None and table_io.is_table_slab(None) is None
+    assert table_io.is_table_slab([(np.zeros((2, 2), np.uint8), np.zeros(3))]) is None               # frame records
+
+
+def test_write_on_file_uses_streaming_writer_and_reference_reader_loads_it(tmp_path):
+    import pickle
+    import rti_b200
+    table = np.arange(4 * 4 * 3 * 3, dtype=np.int32).reshape(4, 4, 3, 3)
+    images = [[table[v, u] for u in range(4)] for v in range(4)]
+    base = str(tmp_path / "interpolation_results_x")
+    rti_b200.write_on_file(images, base, compressed=False)
+    with open(base + ".pickle", "rb") as f:           # what utilities.py:98-99 does
+        back = pickle.load(f)
+    assert all(np.array_equal(back[v][u], table[v, u]) for v in range(4) for u in range(4))
+    back2 = rti_b200.read_from_file(base, compressed=False)
+    assert np.array_equal(back2[3][1], table[3, 1])
+    # anything that is not the table goes through pickle.dump unchanged
+    rti_b200.write_on_file({"a": 1}, str(tmp_path / "other"), compressed=False)
+    assert rti_b200.read_from_file(str(tmp_path / "other"), compressed=False) == {"a": 1}
+    rti_b200.write_on_file(images, str(tmp_path / "z"), compressed=True)
+    assert np.array_equal(rti_b200.read_from_file(str(tmp_path / "z"))[1][2], table[1, 2])
