@@ -227,6 +227,19 @@ int rti_coef_to_f32(const double *d_coef, int64_t n_values, float *d_out, rti_st
 int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, const uint8_t *d_hsv,
                            uint8_t *d_out, rti_stream_t stream);
 
+/* ---- ROI extraction upstream of the path ---------------------------
+ * get_ROI(static_img, points, hsv=True) (Utils/utilities.py:302-342): crop
+ * [y_min, y_min+rows) x [x_min, x_min+cols) out of n_frames BGR frames
+ * uint8 [height][width][3] (frame_stride bytes apart) and convert with OpenCV's
+ * 8-bit COLOR_BGR2HSV integer arithmetic.  hsv != 0: d_out uint8 [rows][cols][3]
+ * per frame (the relighter's HSV ROI, interactive_relighting.py:109); hsv == 0:
+ * only V = max(B,G,R), uint8 [rows][cols] per frame = one frame of the stack that
+ * compute_intensities reads (FeatureMatcher.py:183-184).  out_stride in bytes.
+ * The ROI bounds (centre, clamping quirks) are host arithmetic, see roi.py. */
+int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n_frames, int height,
+                    int width, int x_min, int y_min, int rows, int cols, int hsv,
+                    uint8_t *d_out, int64_t out_stride, rti_stream_t stream);
+
 /* ---- host-buffer pipeline: analysis.compute() steps 2-4 for PTM ---------------------
  * analysis.py:466-472 in one call on HOST buffers: frames uint8 [n][rows_total*cols]
  * and cams float64 [n][3] go in, the slab [row0, row0+rows) is fitted and evaluated,

@@ -18,6 +18,9 @@ citing the reference lines it follows (paths relative to the upstream repo):
     interactive_relighting.py:11-39 + Utils/utilities.py:368-376
                                                    -> cursor_to_light / light_to_index /
                                                       clamp_values / hsv2bgr_u8
+    Utils/utilities.py:272-342 get_corners_center / get_ROI(hsv=True),
+    FeatureMatcher.py:183-184                      -> corners_center / roi_bounds /
+                                                      bgr2hsv_u8 / get_roi_hsv / roi_intensities
 
 Parity pin: the reference has no tests or golden vectors of its own
 (SURVEY.md section 4).  This oracle is pinned instead against outputs of the
@@ -33,6 +36,7 @@ __all__ = [
     "light_axis", "gather_soa", "ptm_design", "ptm_fit", "ptm_grid", "rbf_matrix",
     "rbf_fit", "rbf_grid", "interpolate", "table_from_grids", "cursor_to_light",
     "light_to_index", "clamp_values", "hsv2bgr_u8", "relight_from_table",
+    "corners_center", "roi_bounds", "bgr2hsv_u8", "get_roi_hsv", "roi_intensities",
 ]
 
 
@@ -297,3 +301,68 @@ def relight_from_table(table, hsv_roi, lx: float, ly: float) -> np.ndarray:
     img = np.array(hsv_roi, dtype=np.uint8, copy=True)
     img[:, :, 2] = values
     return hsv2bgr_u8(img)
+
+
+# --------------------------------------------------------------- ROI extraction
+def corners_center(corners, height: int, width: int):
+    """get_corners_center (Utils/utilities.py:272-299): centre of the corners'
+    bounding box, Python round() (half to even) of max - (max - min)/2."""
+    max_x, min_x, max_y, min_y = 0, width, 0, height
+    for x, y in corners:
+        max_x, min_x = max(max_x, x), min(min_x, x)
+        max_y, min_y = max(max_y, y), min(min_y, y)
+    return round(max_x - (max_x - min_x) / 2), round(max_y - (max_y - min_y) / 2)
+
+
+def roi_bounds(shape, corners, roi_diameter: int):
+    """The crop window of get_ROI (Utils/utilities.py:311-327), quirks included:
+    a negative lower bound becomes 1 (not 0), an upper bound past the edge becomes
+    size - 1.  Returns (x_min, x_max, y_min, y_max), upper bounds exclusive."""
+    radius = round(roi_diameter / 2)
+    h, w = shape[0], shape[1]
+    xc, yc = corners_center(np.array(corners), h, w)
+    x_min, x_max, y_min, y_max = xc - radius, xc + radius, yc - radius, yc + radius
+    if x_min < 0:
+        x_min = 1
+    if x_max > w:
+        x_max = w - 1
+    if y_min < 0:
+        y_min = 1
+    if y_max > h:
+        y_max = h - 1
+    return int(x_min), int(x_max), int(y_min), int(y_max)
+
+
+def bgr2hsv_u8(bgr) -> np.ndarray:
+    """8-bit BGR -> HSV with cv2.COLOR_BGR2HSV semantics (Utils/utilities.py:339,
+    H in [0,180)).  OpenCV is third-party to the reference (no version pinned; 4.13.0
+    in the build container); this restates its integer kernel
+        v = max, diff = max - min, s = (diff*sdiv[v] + 2^11) >> 12,
+        h = (v==r ? g-b : v==g ? b-r+2diff : r-g+4diff), h = (h*hdiv[diff] + 2^11) >> 12,
+        h += 180 if h < 0;  sdiv[i] = rint(255*4096/i), hdiv[i] = rint(180*4096/(6i))
+    and was compared with cv2 over all 2^24 colours (tests/golden/make_golden.py)."""
+    bgr = np.asarray(bgr, dtype=np.uint8)
+    b, g, r = (bgr[..., k].astype(np.int64) for k in range(3))
+    v = np.maximum(np.maximum(b, g), r)
+    diff = v - np.minimum(np.minimum(b, g), r)
+    i = np.arange(1, 256, dtype=np.float64)
+    sdiv = np.zeros(256, np.int64)
+    hdiv = np.zeros(256, np.int64)
+    sdiv[1:] = np.rint((255 << 12) / i).astype(np.int64)
+    hdiv[1:] = np.rint((180 << 12) / (6.0 * i)).astype(np.int64)
+    s = (diff * sdiv[v] + (1 << 11)) >> 12
+    h = np.where(v == r, g - b, np.where(v == g, b - r + 2 * diff, r - g + 4 * diff))
+    h = (h * hdiv[diff] + (1 << 11)) >> 12
+    h = h + np.where(h < 0, 180, 0)
+    return np.stack([h, s, v], axis=-1).astype(np.uint8)
+
+
+def get_roi_hsv(img_bgr, corners, roi_diameter: int) -> np.ndarray:
+    """get_ROI(static_img, points, hsv=True) (Utils/utilities.py:302-340)."""
+    x_min, x_max, y_min, y_max = roi_bounds(img_bgr.shape, corners, roi_diameter)
+    return bgr2hsv_u8(np.asarray(img_bgr)[y_min:y_max, x_min:x_max])
+
+
+def roi_intensities(img_bgr, corners, roi_diameter: int) -> np.ndarray:
+    """The frame record's first member: V of the HSV ROI (FeatureMatcher.py:183-184)."""
+    return get_roi_hsv(img_bgr, corners, roi_diameter)[:, :, 2]

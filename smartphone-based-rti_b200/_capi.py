@@ -73,6 +73,7 @@ SIGNATURES = {
     "rti_relight_ptm_f32": (_i, [_p, _l, _l, _f, _f, _p, _p, _p]),
     "rti_coef_to_f32": (_i, [_p, _l, _p, _p]),
     "rti_relight_from_image": (_i, [_p, _l, _p, _p, _p]),
+    "rti_roi_extract": (_i, [_p, _l, _i, _i, _i, _i, _i, _i, _i, _i, _p, _l, _p]),
     "rti_ptm_compute_host": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p, _i]),
     "rti_destroy": (_i, []),
 }

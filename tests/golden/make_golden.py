@@ -13,7 +13,9 @@ Writes
     ref_rbf_n96.npz two pixels of the RBF path at N=96
     relight.npz     cursor->index table of relighting_event / draw_light_roi_position,
                     and a random HSV image with cv2.cvtColor(HSV2BGR) output
-and checks the oracle's HSV->BGR restatement exhaustively against cv2.
+    roi.npz         ut.get_ROI(img, corners, hsv=True) crops of a seeded BGR image
+                    (`make_golden.py roi` regenerates only this one)
+and checks the oracle's HSV->BGR and BGR->HSV restatements exhaustively against cv2.
 """
 import os
 import sys
@@ -67,10 +69,43 @@ def synth_frames(R, N, seed):
     return frames
 
 
+def make_roi_golden(cst, ut, orc):
+    """roi.npz: ut.get_ROI(img, corners, hsv=True) (Utils/utilities.py:302-342) on a seeded
+    BGR image for corner sets that hit every clamping branch; exhaustive BGR2HSV check."""
+    import cv2
+    rng = np.random.default_rng(21)
+    h, w = 90, 120
+    img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    img[10:30, 20:50] = rng.integers(0, 256, (20, 30, 1), dtype=np.uint8)      # grey patch: diff = 0
+    diam = 40
+    cst.ROI_DIAMETER = diam
+    corner_sets = [
+        [(40, 30), (80, 30), (80, 60), (40, 60)],        # interior
+        [(2, 3), (20, 3), (20, 25), (2, 25)],            # x_min, y_min < 0 -> 1
+        [(100, 70), (119, 70), (119, 89), (100, 89)],    # x_max > w, y_max > h -> size - 1
+        [(41, 30), (80, 31), (80, 60), (41, 61)],        # odd extents: round-half-even centre
+        [(0, 40), (40, 40), (40, 50), (0, 50)],          # x_min == 0 exactly (not clamped)
+    ]
+    out = {"img": img, "diameter": np.array(diam), "corners": np.array(corner_sets)}
+    for k, cs in enumerate(corner_sets):
+        roi = ut.get_ROI(img, cs, hsv=True)
+        out["roi%d" % k] = roi
+        mine = orc.get_roi_hsv(img, cs, diam)
+        print("roi case", k, "shape", roi.shape, "oracle equal", np.array_equal(roi, mine))
+    out["cv2_version"] = np.array(cv2.__version__)
+    np.savez_compressed(os.path.join(HERE, "roi.npz"), **out)
+    a = np.arange(1 << 24, dtype=np.uint32)
+    cube = np.stack([a & 255, (a >> 8) & 255, (a >> 16) & 255], -1).astype(np.uint8).reshape(4096, 4096, 3)
+    bad = np.count_nonzero(cv2.cvtColor(cube, cv2.COLOR_BGR2HSV) != orc.bgr2hsv_u8(cube))
+    print("BGR2HSV exhaustive mismatches vs cv2 %s: %d of %d" % (cv2.__version__, bad, cube.size))
+
+
 def main():
     analysis, cst, ut = import_reference()
     sys.path.insert(0, os.path.join(HERE, "..", "..", "oracle"))
     import rti_oracle as orc
+    if sys.argv[1:] == ["roi"]:
+        return make_roi_golden(cst, ut, orc)
 
     # ---- small end-to-end case --------------------------------------------------
     R, N = 6, 40
@@ -144,6 +179,7 @@ def main():
     print("rbf grid max rel diff",
           max(np.max(np.abs(og[y, x] - rbf[y][x])) / np.max(np.abs(rbf[y][x])) for y, x in keep))
     print("rbf table mismatches", np.count_nonzero(orc.table_from_grids(og) != tab_rbf))
+    make_roi_golden(cst, ut, orc)
 
 
 if __name__ == "__main__":
