@@ -151,8 +151,12 @@ def compute_intensities(data, first_only=False):
         raise Exception("Error computing intensities: results are empty")
     print("Computing intensities values:")
     range_val = 1 if first_only else _cst.ROI_DIAMETER
-    frames, cams = _stack_frames(data, range_val, range_val)
-    soa = _SoA(FrameStack(frames, cams))
+    torch = _torch()
+    from . import ingest
+    frames, cams = ingest.pinned_stack(data, range_val, range_val)      # one copy, into pinned memory
+    stack = FrameStack.from_device(frames.cuda(non_blocking=True), torch.from_numpy(cams).cuda())
+    stack._pinned = frames                                               # alive until the upload has run
+    soa = _SoA(stack)
     return (DeviceArrayView(soa, 0), DeviceArrayView(soa, 1), DeviceArrayView(soa, 2))
 
 
@@ -551,8 +555,10 @@ def read_from_file(filename, compressed=True):
     if not os.path.isfile(filename):
         raise Exception("Storage file not found!")
     print("Reading from file {}".format(filename))
-    opener = bz2.BZ2File if compressed else open
-    with opener(filename, "rb") as f:
+    if compressed:
+        from . import ingest
+        return ingest.read_pbz2(filename)        # same object, bzip2 blocks decoded in parallel
+    with open(filename, "rb") as f:
         return pickle.load(f)
 
 
@@ -591,7 +597,7 @@ def compute(video_name="coin1", from_storage=False, storage_filepath=None, inter
     return results_images
 
 
-def install(analysis_module, constants_module=None, fast_writer=True):
+def install(analysis_module, constants_module=None, fast_writer=True, fast_reader=True):
     """Drop-in: rebind the reference module's hot functions to this implementation.
 
     analysis.compute() resolves compute_intensities / interpolate_intensities /
@@ -622,4 +628,17 @@ def install(analysis_module, constants_module=None, fast_writer=True):
         write_on_file_fast._rti_b200 = True
         write_on_file_fast._original = original
         ut.write_on_file = write_on_file_fast
+    # analysis.compute(from_storage=True) loads the frame list with ut.read_from_file (analysis.py:434)
+    if fast_reader and ut is not None and hasattr(ut, "read_from_file") \
+            and not getattr(ut.read_from_file, "_rti_b200", False):
+        original_reader = ut.read_from_file
+
+        def read_from_file_fast(filename, compressed=True):
+            if not compressed:
+                return original_reader(filename, compressed=compressed)
+            return read_from_file(filename, compressed=True)
+
+        read_from_file_fast._rti_b200 = True
+        read_from_file_fast._original = original_reader
+        ut.read_from_file = read_from_file_fast
     return analysis_module
