@@ -11,6 +11,7 @@ namespace rti {
 void set_error(const char *fmt, ...);
 int check_cuda(cudaError_t e, const char *what);
 void count_launch(int n = 1);
+void release_tile_counters();      // ptm_fused.cu: frees the dynamic-scheduler counters (rti_destroy)
 
 #define RTI_REQUIRE(cond, ...)                 \
     do {                                       \
@@ -71,6 +72,14 @@ __device__ __forceinline__ void light_vector(double cx, double cy, double cz2, d
     ly = (float)(dy * r);
 }
 
+// Note on the float32 roundings of the fit (two f64->f32 and five f32->f64 conversions per light
+// sample, all XU-pipe instructions at 16 lanes/clk/SM): doing them on the integer pipe instead
+// (round-to-nearest-even on the fp64 bit pattern, 7 ALU instructions each) was measured and is
+// SLOWER on sm_100 (fit 2.05 -> 2.22 ms at 1M pixels x 500 lights): the ALU pipe has the same
+// 16 lanes/clk/SMSP as the fp64 pipe and the instruction count doubles.  The conversions stay.
+// Likewise the table's F2I: replacing it by an add.rz.f64 magic-number truncation + 3 integer
+// instructions was neutral for the table kernel and slower inside the fused kernels.
+
 // The 26 running sums of one pixel's normal equations for the design row
 // m = (u2, v2, uv, u, v, 1) (analysis.py:285) and right-hand side I:
 //   g[0..14]  sum m_a*m_b for a <= b < 5 (row-major upper triangle of the 5x5 block)
@@ -97,6 +106,9 @@ struct NormalEq {
         m[2] = (double)__fmul_rn(lu, lv);
         m[3] = (double)lu;
         m[4] = (double)lv;
+        accumulate(m, inten);
+    }
+    __device__ __forceinline__ void accumulate(const double m[5], double inten) {
         int k = 0;
 #pragma unroll
         for (int a = 0; a < 5; ++a) {

@@ -98,8 +98,9 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
         if (tile_rows < 1) tile_rows = 1;
     }
     if (tile_rows > rows) tile_rows = rows;
-    // keep tile pixel counts a multiple of 4 so the table kernel can use 16-byte stores
-    while (tile_rows < rows && ((int64_t)tile_rows * cols) % 4 != 0) ++tile_rows;
+    // keep tile pixel counts a multiple of 16: 16-byte table stores, and 16-byte aligned frame rows
+    // on the device, which the warp-specialised fused kernel's cp.async staging needs
+    while (tile_rows < rows && ((int64_t)tile_rows * cols) % 16 != 0) ++tile_rows;
     const int64_t tile_pixels = (int64_t)tile_rows * cols;
     const int64_t slab_pixels = (int64_t)rows * cols;
     const int64_t frame_pitch = (int64_t)rows_total * cols;
@@ -172,6 +173,7 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
 }
 
 extern "C" int rti_destroy(void) {
+    release_tile_counters();
     std::lock_guard<std::mutex> lock(g_pipe_mutex);
     return pipe_release(g_pipe);
 }

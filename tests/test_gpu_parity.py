@@ -617,6 +617,41 @@ def test_fused_kernel_equals_two_kernel_path(torch_cuda, rows, cols, n, row0, g_
     assert torch.equal(table, table2)
 
 
+@pytest.mark.parametrize("rows,cols,n,row0,g_step", [
+    (5, 103, 77, 2, 0.1),        # 3 tiles, the last with 3 pixels; 2 frame chunks (64 + 13)
+    (1, 16, 6, 0, 0.5),          # one partial tile, fewest lights
+    (4, 64, 64, 0, 0.25),        # exactly one tile and one full chunk
+    (3, 257, 200, 5, 0.25),      # 4 chunks (ring wraps), partial tile
+    (451, 256, 70, 3, 0.25),     # 451 tiles on <= 148 persistent CTAs: >= 3 tiles each (buffer hand-back)
+    (37, 1000, 130, 0, 0.5),     # 145 tiles: fewer tiles than SMs
+])
+def test_fused_ws_kernel_padded_stride(torch_cuda, rows, cols, n, row0, g_step):
+    """The warp-specialised persistent kernel (taken for 16-byte aligned frame rows) against the
+    two-kernel path, bit for bit, with a padded frame stride so partial tiles are exercised."""
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    frames, cams = synthetic.lambertian_stack(rows, cols, n, seed=5 * n + rows, row0=row0, rows_total=rows + row0)
+    ax = orc.light_axis(g_step)
+    g = ax.size
+    p = rows * cols
+    stride = (p + 15) // 16 * 16 + 16
+    padded = np.full((n, stride), 255, dtype=np.uint8)
+    padded[:, :p] = frames.reshape(n, p)
+    d_f, d_c, d_ax = dev(torch, padded), dev(torch, cams), dev(torch, ax)
+    coef, bad = gpu_fit_frames(torch, frames, cams, row0=row0)
+    table = torch.empty((g, g, p), dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_table", coef.data_ptr(), p, p, d_ax.data_ptr(), g, table.data_ptr(), p, None, None)
+    coef2 = torch.empty_like(coef)
+    table2 = torch.full_like(table, -7)
+    bad2 = torch.zeros(2, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_table_frames", d_f.data_ptr(), stride, d_c.data_ptr(), n, row0, rows, cols, d_ax.data_ptr(),
+               g, coef2.data_ptr(), p, table2.data_ptr(), p, bad2.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert bad == 0 and bad2.sum().item() == 0
+    assert torch.equal(coef, coef2)
+    assert torch.equal(table, table2)
+
+
 def test_fused_kernel_reference_golden(torch_cuda, ref_small):
     from rti_b200 import _capi
     torch = torch_cuda
