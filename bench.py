@@ -398,7 +398,7 @@ def run_gpu(args, rank, local_rank, world):
     alg_bytes = table_bytes + units_per_rank + 48 * p        # int32 table + uint8 frames + coefficient map
     achieved = alg_bytes / (fused_ms * 1e-3) / 1e9
     tbl_bytes = table_bytes + 48 * p
-    roofline = {"bound": "hbm", "kernel": "ptm_fused_kernel<true>", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": "ptm_fused_ws_kernel<true>", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": read_traffic(), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "launch_ms": fused_ms,
                 "two_kernel_form": {
