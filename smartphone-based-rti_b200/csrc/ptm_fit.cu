@@ -198,6 +198,7 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
 // --------------------------------------------------------------------------------------
 constexpr int SH_THREADS = 128;
 constexpr int SH_CHUNK = 256;
+constexpr int SH_UNROLL = 16;
 
 __global__ void __launch_bounds__(SH_THREADS)
 ptm_fit_shared_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
@@ -219,24 +220,37 @@ ptm_fit_shared_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
             s_p[i / 6][i % 6] = pinv[(int64_t)(i % 6) * n + f0 + i / 6];
         __syncthreads();
         if (p0 >= n_pixels) continue;
-        for (int i = 0; i < fc; ++i) {
+        // SH_UNROLL frame words are requested before the first is used: the kernel is a stream of
+        // 4-byte loads with 24 DFMAs each, and without the batch it is bound by load latency
+        auto load_word = [&](int i) -> uint32_t {
             const uint8_t *src = frames + (int64_t)(f0 + i) * frame_stride + p0;
-            uint32_t w;
-            if (vec) {
-                w = __ldg(reinterpret_cast<const uint32_t *>(src));
-            } else {
-                w = 0;
+            if (vec) return __ldg(reinterpret_cast<const uint32_t *>(src));
+            uint32_t w = 0;
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    if (p0 + q < n_pixels) w |= (uint32_t)__ldg(src + q) << (8 * q);
-            }
+            for (int q = 0; q < 4; ++q)
+                if (p0 + q < n_pixels) w |= (uint32_t)__ldg(src + q) << (8 * q);
+            return w;
+        };
+        auto accumulate = [&](int i, uint32_t w) {
+            double pk[6];
+#pragma unroll
+            for (int k = 0; k < 6; ++k) pk[k] = s_p[i][k];
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const double v = (double)((w >> (8 * q)) & 0xffu);
+                const double v = u8_to_double((w >> (8 * q)) & 0xffu);     // no I2F (XU pipe)
 #pragma unroll
-                for (int k = 0; k < 6; ++k) acc[q][k] = fma(s_p[i][k], v, acc[q][k]);
+                for (int k = 0; k < 6; ++k) acc[q][k] = fma(pk[k], v, acc[q][k]);
             }
+        };
+        int i = 0;
+        for (; i + SH_UNROLL <= fc; i += SH_UNROLL) {
+            uint32_t w[SH_UNROLL];
+#pragma unroll
+            for (int j = 0; j < SH_UNROLL; ++j) w[j] = load_word(i + j);
+#pragma unroll
+            for (int j = 0; j < SH_UNROLL; ++j) accumulate(i + j, w[j]);
         }
+        for (; i < fc; ++i) accumulate(i, load_word(i));
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q)

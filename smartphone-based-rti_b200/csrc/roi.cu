@@ -11,9 +11,9 @@
 //   h = (h * hdiv[diff] + 2^11) >> 12 (arithmetic shift), h += 180 if h < 0,
 //                                                   hdiv[i] = rint(180 * 4096 / (6 i))
 // The op is a byte stream: 3 B read + 1 B (V) or 3 B (HSV) written per ROI pixel, HBM-bound.
-// One CTA converts a run of 1024 pixels of one ROI row: the run's bytes are staged in shared
+// One CTA converts runs of 1024 pixels of four ROI rows: the runs' bytes are staged in shared
 // memory with 16-byte loads (rows start at arbitrary byte offsets inside the frame), each
-// thread then converts 4 consecutive pixels and stores them as one 4-byte / three 4-byte words.
+// thread then converts 4 consecutive pixels per row and stores them as one / three 4-byte words.
 #include "common.cuh"
 
 namespace rti {
@@ -21,7 +21,7 @@ namespace rti {
 constexpr int ROI_THREADS = 256;
 constexpr int ROI_PIX_PER_THREAD = 4;
 constexpr int ROI_TILE = ROI_THREADS * ROI_PIX_PER_THREAD;       // pixels per CTA
-constexpr int ROI_STAGE_BYTES = ROI_TILE * 3 + 32;               // + alignment slack both ends
+constexpr int ROI_STAGE_BYTES = ROI_TILE * 3 + 48;               // + alignment slack both ends, word over-read
 
 __device__ __forceinline__ uint4 ld_stream_v4(const void *p) {
     uint4 v;
@@ -30,19 +30,22 @@ __device__ __forceinline__ uint4 ld_stream_v4(const void *p) {
     return v;
 }
 
+constexpr int ROI_ROWS = 4;                                      // ROI rows per CTA (bytes in flight)
+
 template <bool HSV>
 __global__ void __launch_bounds__(ROI_THREADS)
 roi_extract_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride, int64_t row_pitch,
                    int x_min, int y_min, int rows, int cols, uint8_t *__restrict__ out,
                    int64_t out_stride) {
-    __shared__ __align__(16) uint8_t stage[ROI_STAGE_BYTES];
+    __shared__ __align__(16) uint8_t stage[ROI_ROWS][ROI_STAGE_BYTES];
     __shared__ int sdiv[HSV ? 256 : 1];
     __shared__ int hdiv[HSV ? 256 : 1];
     const int tid = threadIdx.x;
     const int x0 = blockIdx.x * ROI_TILE;                        // first ROI column of the run
-    const int y = blockIdx.y;
+    const int y0 = blockIdx.y * ROI_ROWS;
     const int64_t f = blockIdx.z;
     const int npix = min(ROI_TILE, cols - x0);
+    const int nrows = min(ROI_ROWS, rows - y0);
 
     if (HSV) {
         // tables as OpenCV builds them: saturate_cast<int>(x) = rint(x) for doubles
@@ -51,60 +54,78 @@ roi_extract_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride, int
         hdiv[i] = i ? __double2int_rn((double)(180 << 12) / (6.0 * (double)i)) : 0;
     }
 
-    // ---- stage [a0, a1) of the frame through 16-byte granules
-    const uint8_t *src = frames + f * frame_stride + (int64_t)(y_min + y) * row_pitch + (int64_t)(x_min + x0) * 3;
-    const uintptr_t a0 = (uintptr_t)src;
-    const uintptr_t a1 = a0 + (uintptr_t)npix * 3;
-    const uintptr_t g0 = a0 & ~(uintptr_t)15;
-    const int skew = (int)(a0 - g0);                             // stage[skew] = first byte of the run
-    const int ngran = (int)((a1 - g0 + 15) >> 4);
-    for (int gi = tid; gi < ngran; gi += ROI_THREADS) {
-        const uintptr_t ga = g0 + ((uintptr_t)gi << 4);
-        if (ga >= a0 && ga + 16 <= a1) {
-            *reinterpret_cast<uint4 *>(stage + (gi << 4)) = ld_stream_v4((const void *)ga);
-        } else {                                                 // first / last partial granule
-            for (int k = 0; k < 16; ++k) {
-                const uintptr_t a = ga + k;
-                if (a >= a0 && a < a1) stage[(gi << 4) + k] = *(const uint8_t *)a;
+    // ---- stage [a0, a1) of every row through 16-byte granules; all rows' loads are issued
+    // before the barrier so one CTA keeps up to 12 KB in flight
+    const uint8_t *src0 = frames + f * frame_stride + (int64_t)(y_min + y0) * row_pitch + (int64_t)(x_min + x0) * 3;
+#pragma unroll
+    for (int r = 0; r < ROI_ROWS; ++r) {
+        if (r >= nrows) continue;
+        const uintptr_t a0 = (uintptr_t)(src0 + r * row_pitch);
+        const uintptr_t a1 = a0 + (uintptr_t)npix * 3;
+        const uintptr_t g0 = a0 & ~(uintptr_t)15;                // stage[r][a0 - g0] = first byte of the run
+        const int ngran = (int)((a1 - g0 + 15) >> 4);
+        for (int gi = tid; gi < ngran; gi += ROI_THREADS) {
+            const uintptr_t ga = g0 + ((uintptr_t)gi << 4);
+            if (ga >= a0 && ga + 16 <= a1) {
+                *reinterpret_cast<uint4 *>(&stage[r][gi << 4]) = ld_stream_v4((const void *)ga);
+            } else {                                             // first / last partial granule
+                for (int k = 0; k < 16; ++k) {
+                    const uintptr_t a = ga + k;
+                    if (a >= a0 && a < a1) stage[r][(gi << 4) + k] = *(const uint8_t *)a;
+                }
             }
         }
     }
     __syncthreads();
 
-    // ---- convert 4 pixels per thread
+    // ---- convert 4 pixels per thread and row: the thread's 12 bytes start at skew + 12 tid, i.e.
+    // (skew & 3) bytes into a 32-bit word for every thread of the row: 4 word loads + funnel shifts
     const int p0 = tid * ROI_PIX_PER_THREAD;
     if (p0 >= npix) return;
     const int cnt = min(ROI_PIX_PER_THREAD, npix - p0);
-    uint8_t res[ROI_PIX_PER_THREAD * (HSV ? 3 : 1)];
-#pragma unroll
-    for (int k = 0; k < ROI_PIX_PER_THREAD; ++k) {
-        const uint8_t *px = stage + skew + (p0 + (k < cnt ? k : 0)) * 3;
-        const int b = px[0], g = px[1], r = px[2];
-        const int v = max(max(b, g), r);
-        if (HSV) {
-            const int diff = v - min(min(b, g), r);
-            const int s = (diff * sdiv[v] + (1 << 11)) >> 12;
-            int h = (v == r) ? (g - b) : (v == g) ? (b - r + 2 * diff) : (r - g + 4 * diff);
-            h = (h * hdiv[diff] + (1 << 11)) >> 12;
-            h += h < 0 ? 180 : 0;
-            res[3 * k + 0] = (uint8_t)h;
-            res[3 * k + 1] = (uint8_t)s;
-            res[3 * k + 2] = (uint8_t)v;
-        } else {
-            res[k] = (uint8_t)v;
-        }
-    }
     constexpr int BPP = HSV ? 3 : 1;
-    uint8_t *dst = out + f * out_stride + ((int64_t)y * cols + x0 + p0) * BPP;
-    if (cnt == ROI_PIX_PER_THREAD && ((uintptr_t)dst & 3) == 0) {
 #pragma unroll
-        for (int w = 0; w < BPP; ++w) {
-            const uint32_t word = (uint32_t)res[4 * w] | ((uint32_t)res[4 * w + 1] << 8) |
-                                  ((uint32_t)res[4 * w + 2] << 16) | ((uint32_t)res[4 * w + 3] << 24);
-            reinterpret_cast<uint32_t *>(dst)[w] = word;
+    for (int r = 0; r < ROI_ROWS; ++r) {
+        if (r >= nrows) continue;
+        const int o = (int)((uintptr_t)(src0 + r * row_pitch) & 15) + p0 * 3;
+        const uint32_t *wsrc = reinterpret_cast<const uint32_t *>(&stage[r][o & ~3]);
+        const unsigned sh = (unsigned)(o & 3) * 8u;
+        const uint32_t w0 = wsrc[0], w1 = wsrc[1], w2 = wsrc[2], w3 = wsrc[3];
+        uint32_t in[3];
+        in[0] = __funnelshift_r(w0, w1, sh);
+        in[1] = __funnelshift_r(w1, w2, sh);
+        in[2] = __funnelshift_r(w2, w3, sh);
+        uint8_t res[ROI_PIX_PER_THREAD * BPP];
+#pragma unroll
+        for (int k = 0; k < ROI_PIX_PER_THREAD; ++k) {
+            const int b = (in[(3 * k) >> 2] >> (8 * ((3 * k) & 3))) & 0xff;
+            const int g = (in[(3 * k + 1) >> 2] >> (8 * ((3 * k + 1) & 3))) & 0xff;
+            const int rr = (in[(3 * k + 2) >> 2] >> (8 * ((3 * k + 2) & 3))) & 0xff;
+            const int v = max(max(b, g), rr);
+            if (HSV) {
+                const int diff = v - min(min(b, g), rr);
+                const int sat = (diff * sdiv[v] + (1 << 11)) >> 12;
+                int h = (v == rr) ? (g - b) : (v == g) ? (b - rr + 2 * diff) : (rr - g + 4 * diff);
+                h = (h * hdiv[diff] + (1 << 11)) >> 12;
+                h += h < 0 ? 180 : 0;
+                res[3 * k + 0] = (uint8_t)h;
+                res[3 * k + 1] = (uint8_t)sat;
+                res[3 * k + 2] = (uint8_t)v;
+            } else {
+                res[k] = (uint8_t)v;
+            }
         }
-    } else {
-        for (int k = 0; k < cnt * BPP; ++k) dst[k] = res[k];
+        uint8_t *dst = out + f * out_stride + ((int64_t)(y0 + r) * cols + x0 + p0) * BPP;
+        if (cnt == ROI_PIX_PER_THREAD && ((uintptr_t)dst & 3) == 0) {
+#pragma unroll
+            for (int w = 0; w < BPP; ++w) {
+                const uint32_t word = (uint32_t)res[4 * w] | ((uint32_t)res[4 * w + 1] << 8) |
+                                      ((uint32_t)res[4 * w + 2] << 16) | ((uint32_t)res[4 * w + 3] << 24);
+                reinterpret_cast<uint32_t *>(dst)[w] = word;
+            }
+        } else {
+            for (int k = 0; k < cnt * BPP; ++k) dst[k] = res[k];
+        }
     }
 }
 
@@ -125,7 +146,7 @@ extern "C" int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n
     const int64_t bpp = hsv ? 3 : 1;
     RTI_REQUIRE(frame_stride >= (int64_t)height * width * 3 || n_frames == 1, "rti_roi_extract: frame stride too small");
     RTI_REQUIRE(out_stride >= (int64_t)rows * cols * bpp || n_frames == 1, "rti_roi_extract: output stride too small");
-    dim3 grid((cols + ROI_TILE - 1) / ROI_TILE, rows, n_frames);
+    dim3 grid((cols + ROI_TILE - 1) / ROI_TILE, (rows + ROI_ROWS - 1) / ROI_ROWS, n_frames);
     const int64_t pitch = (int64_t)width * 3;
     if (hsv)
         roi_extract_kernel<true><<<grid, ROI_THREADS, 0, as_stream(stream)>>>(d_bgr, frame_stride, pitch, x_min, y_min,

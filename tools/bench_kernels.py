@@ -111,9 +111,24 @@ def main():
     pinv = torch.from_numpy(np.random.default_rng(0).normal(0, 1, (6, n))).cuda()
     ms, best = tm.run(lambda: _capi.call("rti_ptm_fit_shared", d_f.data_ptr(), p, pinv.data_ptr(), n, p,
                                          coef.data_ptr(), p, S), flush=False)
-    hbm_line("ptm_fit_shared_kernel", [p, n], ms, best, p * n + 48 * p, units_per_s=p * n / (ms * 1e-3),
-             dfma_per_s=6 * p * n / (ms * 1e-3))
+    # 6 DFMA per byte read: fp64-pipe bound (measured DFMA peak 18.5e12/s, profiles/r01_peak_fp64.jsonl)
+    emit(kernel="ptm_fit_shared_kernel", shape=[p, n], ms=ms, ms_best=best, bound="fp64 pipe",
+         units_per_s=p * n / (ms * 1e-3), dfma_per_s=6 * p * n / (ms * 1e-3),
+         frac_of_dfma_peak=6 * p * n / (ms * 1e-3) / 18.5e12, achieved_gbs=(p * n + 48 * p) / (ms * 1e-3) / 1e9)
     del d_f
+
+    # ---------------------------------------------------------------- ROI extraction (rows f2 / f4)
+    fh, fw, nf, roi = (2160, 3840, 40, 2048) if not args.quick else (1080, 1920, 8, 400)
+    bgr = torch.randint(0, 256, (nf, fh, fw, 3), dtype=torch.uint8, device="cuda")
+    x0, y0 = (fw - roi) // 2 + 1, (fh - roi) // 2 + 1
+    for hsv_flag, bpp in ((0, 1), (1, 3)):
+        o = torch.empty((nf, roi, roi, bpp), dtype=torch.uint8, device="cuda")
+        ms, best = tm.run(lambda: _capi.call("rti_roi_extract", bgr.data_ptr(), fh * fw * 3, nf, fh, fw, x0, y0, roi, roi,
+                                             hsv_flag, o.data_ptr(), roi * roi * bpp, S))
+        hbm_line("roi_extract_kernel<%s>" % ("hsv" if hsv_flag else "V"), [nf, roi, roi], ms, best,
+                 (3 + bpp) * nf * roi * roi, frames_per_s=nf / (ms * 1e-3))
+        del o
+    del bgr
 
     # ---------------------------------------------------------------- fp64 grids + grids->table (rows a3, a6)
     axis = rti_b200.light_axis(0.02)
