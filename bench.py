@@ -420,7 +420,7 @@ def run_gpu(args, rank, local_rank, world):
         "kernel_ms": {"ptm_fused": fused_ms, "ptm_fit_frames": fit_ms, "ptm_table": table_ms},
         "secondary": secondary,
     }
-    print(json.dumps(line), flush=True)
+    return line
 
 
 def main():
@@ -450,7 +450,19 @@ def main():
                    "--master-addr", "127.0.0.1", "--master-port", "29531", os.path.abspath(__file__)] + sys.argv[1:]
             sys.exit(subprocess.call(cmd))
         raise SystemExit("WORLD_SIZE=%d but --gpus %d" % (world, args.gpus))
-    run_gpu(args, rank, local_rank, world)
+    # Native libraries (NCCL prints its version banner) write to fd 1; the contract is ONE JSON line on
+    # stdout, so everything but the final line goes to stderr.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        line = run_gpu(args, rank, local_rank, world)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    if line is not None:
+        print(json.dumps(line), flush=True)
     if world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
