@@ -666,3 +666,42 @@ def test_fused_kernel_reference_golden(torch_cuda, ref_small):
     torch.cuda.synchronize()
     assert bad.sum().item() == 0
     assert np.array_equal(table.cpu().numpy().reshape(100, 100, rows, cols), ref_small["table_ptm"])
+
+
+def test_fused_ws_kernel_stays_inside_its_buffers(torch_cuda):
+    """compute-sanitizer is not available on the GPU pool: guard bands around every output of the
+    persistent kernel (partial last tile, padded strides) must come back untouched, and the frame
+    reads must not need anything past the last valid byte (the stack is allocated exactly)."""
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    rows, cols, n, g = 7, 131, 70, 8              # 917 pixels: 4 tiles, last one with 149 pixels
+    p = rows * cols
+    frames, cams = synthetic.lambertian_stack(rows, cols, n, seed=8)
+    stride = (p + 15) // 16 * 16
+    flat = torch.zeros(n * stride - (stride - p), dtype=torch.uint8, device="cuda")   # ends at the last valid byte
+    for i in range(n):
+        flat[i * stride:i * stride + p] = torch.from_numpy(frames[i].reshape(-1)).cuda()
+    ax = orc.light_axis(0.25)
+    d_c, d_ax = dev(torch, cams), dev(torch, ax)
+    guard = 64
+    plane, image = p + 5, p + 12                  # strides larger than the pixel count
+    coef = torch.full((guard + 6 * plane + guard,), -777.0, dtype=torch.float64, device="cuda")
+    table = torch.full((guard + g * g * image + guard,), -777, dtype=torch.int32, device="cuda")
+    bad = torch.zeros(2 + 2 * guard, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_table_frames", flat.data_ptr(), stride, d_c.data_ptr(), n, 0, rows, cols, d_ax.data_ptr(),
+               g, coef.data_ptr() + 8 * guard, plane, table.data_ptr() + 4 * guard, image,
+               bad.data_ptr() + 4 * guard, None)
+    torch.cuda.synchronize()
+    assert bad.sum().item() == 0
+    c = coef.cpu().numpy()
+    t = table.cpu().numpy()
+    assert np.all(c[:guard] == -777.0) and np.all(c[-guard:] == -777.0)
+    assert np.all(t[:guard] == -777) and np.all(t[-guard:] == -777)
+    cv = c[guard:-guard].reshape(6, plane)
+    tv = t[guard:-guard].reshape(g * g, image)
+    assert np.all(cv[:, p:] == -777.0) and np.all(tv[:, p:] == -777)        # stride padding untouched
+    lx, ly, inten = orc.gather_soa(frames, cams)
+    ref = orc.ptm_fit_batch(lx, ly, inten).reshape(p, 6).T
+    assert np.abs(cv[:, :p] - ref).max() <= PTM_COEF_RTOL * np.abs(ref).max()
+    want = orc.table_from_grids(orc.ptm_grid(ref.T.reshape(rows, cols, 6), ax)).reshape(g * g, p)
+    assert np.array_equal(tv[:, :p], want)

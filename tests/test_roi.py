@@ -143,3 +143,27 @@ def test_gpu_roi_argument_errors(torch_cuda):
         _capi.call("rti_roi_extract", d.data_ptr(), 300, 1, 10, 10, 5, 0, 10, 10, 1, o.data_ptr(), 300, None)
     with pytest.raises(_capi.RtiError):
         _capi.call("rti_roi_extract", None, 300, 1, 10, 10, 0, 0, 10, 10, 1, o.data_ptr(), 300, None)
+
+
+@pytest.mark.gpu
+def test_gpu_roi_stays_inside_its_buffers(torch_cuda):
+    """Guard bands (no compute-sanitizer on the pool): the frame is allocated exactly, the ROI touches its
+    last byte, and nothing outside the output is written."""
+    torch = torch_cuda
+    from rti_b200 import _capi
+    rng = np.random.default_rng(3)
+    h, w = 21, 37
+    frame = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+    d = torch.from_numpy(frame).cuda()
+    for hsv, bpp in ((0, 1), (1, 3)):
+        rows, cols, x0, y0 = 9, 30, 7, 12                     # ends at the frame's last pixel
+        guard = 256
+        out = torch.full((guard + rows * cols * bpp + guard,), 0xAB, dtype=torch.uint8, device="cuda")
+        _capi.call("rti_roi_extract", d.data_ptr(), h * w * 3, 1, h, w, x0, y0, rows, cols, hsv,
+                   out.data_ptr() + guard, rows * cols * bpp, None)
+        torch.cuda.synchronize()
+        o = out.cpu().numpy()
+        assert np.all(o[:guard] == 0xAB) and np.all(o[-guard:] == 0xAB)
+        want = orc.bgr2hsv_u8(frame[y0:y0 + rows, x0:x0 + cols])
+        want = want if hsv else want[:, :, 2]
+        assert np.array_equal(o[guard:-guard].reshape(want.shape), want)
