@@ -69,26 +69,72 @@ def _array_template(shape, dtype):
 
 
 def is_table_slab(images):
-    """The (G, G, R, R) base array if `images` is the nested list of views that
-    prepare_images_data returns (every images[v][u] is base[v, u]), else None."""
+    """A C-contiguous (G_v, G_u, rows, cols) ndarray over the images' own memory if `images` is a nested
+    list of equally shaped views laid out back to back in one buffer (what prepare_images_data
+    returns: every images[v][u] is a view of one host slab), else None."""
     try:
         first = images[0][0]
         base = first.base
-        if base is None or not isinstance(base, np.ndarray) or base.ndim != 4 or not base.flags.c_contiguous:
+        gv, gu = len(images), len(images[0])
+        if base is None or not isinstance(first, np.ndarray) or not first.flags.c_contiguous or first.ndim != 2:
             return None
-        if len(images) != base.shape[0] or any(len(row) != base.shape[1] for row in images):
+        if any(len(row) != gu for row in images):
             return None
-        step = base.strides[1]
-        addr0 = base.__array_interface__["data"][0]
-        for v in (0, len(images) - 1):
-            for u in (0, len(images[v]) - 1):
+        nb = first.nbytes
+        addr0 = first.__array_interface__["data"][0]
+        for v in range(gv):
+            for u in range(gu):
                 a = images[v][u]
-                if a.base is not base or a.shape != base.shape[2:] or a.dtype != base.dtype \
-                        or a.__array_interface__["data"][0] != addr0 + (v * base.shape[1] + u) * step:
+                if not isinstance(a, np.ndarray) or a.base is not base or a.shape != first.shape \
+                        or a.dtype != first.dtype or not a.flags.c_contiguous \
+                        or a.__array_interface__["data"][0] != addr0 + (v * gu + u) * nb:
                     return None
-        return base
+        return np.lib.stride_tricks.as_strided(first, shape=(gv, gu) + first.shape,
+                                               strides=(gu * nb, nb) + first.strides, writeable=False)
     except Exception:
         return None
+
+
+class TableStreamWriter:
+    """Push-style writer of the protocol-4 pickle of ``[[img(v, u) for u in range(gu)] for v in
+    range(gv)]``: ``write_images(block)`` takes the next images in row-major order as a C-contiguous
+    (count, ...) array (or any sequence of buffers) and writes them at once, so the source may be a
+    pinned staging buffer that the next device-to-host copy refills; ``close()`` terminates the pickle."""
+
+    def __init__(self, gv, gu, image_shape, dtype, fileobj):
+        self.gv, self.gu = int(gv), int(gu)
+        self.prefix, self.suffix = _array_template(tuple(image_shape), np.dtype(dtype))
+        self.w = fileobj.write
+        self.count = 0
+        self.w(pickle.PROTO + bytes([_PROTO]))
+        self.w(pickle.EMPTY_LIST)
+        if self.gv:
+            self.w(pickle.MARK)
+        if self.gu == 0:                       # rows without images
+            for _ in range(self.gv):
+                self.w(pickle.EMPTY_LIST)
+
+    def write_images(self, block):
+        w, gu = self.w, self.gu
+        for img in block:
+            if self.count >= self.gv * gu:
+                raise ValueError("more images than gv * gu")
+            if self.count % gu == 0:
+                w(pickle.EMPTY_LIST)
+                w(pickle.MARK)
+            w(self.prefix)
+            w(memoryview(np.ascontiguousarray(img)).cast("B"))
+            w(self.suffix)
+            self.count += 1
+            if self.count % gu == 0:
+                w(pickle.APPENDS)
+
+    def close(self):
+        if self.count != self.gv * self.gu:
+            raise ValueError("table incomplete: %d of %d images written" % (self.count, self.gv * self.gu))
+        if self.gv:
+            self.w(pickle.APPENDS)
+        self.w(pickle.STOP)
 
 
 def dump_table(table, fileobj):
@@ -98,25 +144,9 @@ def dump_table(table, fileobj):
     ``pickle.dump([[table[v, u] for u in range(G_u)] for v in range(G_v)], fileobj)``."""
     table = np.ascontiguousarray(table)
     gv, gu = table.shape[:2]
-    prefix, suffix = _array_template(table.shape[2:], table.dtype)
-    flat = table.reshape(gv, gu, -1)
-    w = fileobj.write
-    w(pickle.PROTO + bytes([_PROTO]))
-    w(pickle.EMPTY_LIST)
-    if gv:
-        w(pickle.MARK)
-    for v in range(gv):
-        w(pickle.EMPTY_LIST)
-        if gu:
-            w(pickle.MARK)
-            for u in range(gu):
-                w(prefix)
-                w(memoryview(flat[v, u]).cast("B"))
-                w(suffix)
-            w(pickle.APPENDS)
-    if gv:
-        w(pickle.APPENDS)
-    w(pickle.STOP)
+    writer = TableStreamWriter(gv, gu, table.shape[2:], table.dtype, fileobj)
+    writer.write_images(table.reshape((gv * gu,) + table.shape[2:]))
+    writer.close()
 
 
 def dumps_table(table) -> bytes:

@@ -118,7 +118,13 @@ def test_dump_table_round_trips_like_pickle_dump(tmp_path):
     rng = np.random.default_rng(0)
     table = rng.integers(-500, 500, (5, 7, 6, 6)).astype(np.int32)
     images = [[table[v, u] for u in range(7)] for v in range(5)]
-    assert table_io.is_table_slab(images) is table
+    slab = table_io.is_table_slab(images)
+    assert slab.shape == table.shape and np.shares_memory(slab, table) and np.array_equal(slab, table)
+    # the same images over a flat 2-D host buffer (how prepare_images_data assembles them) are recognised too
+    flat = table.reshape(35, 36).copy()
+    views = flat.reshape(5, 7, 6, 6)
+    slab2 = table_io.is_table_slab([[views[v, u] for u in range(7)] for v in range(5)])
+    assert slab2 is not None and np.shares_memory(slab2, flat) and np.array_equal(slab2, table)
     out = pickle.loads(table_io.dumps_table(table))
     ref = pickle.loads(pickle.dumps(images))
     assert type(out) is list and len(out) == 5 and all(type(r) is list and len(r) == 7 for r in out)
