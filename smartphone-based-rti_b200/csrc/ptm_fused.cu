@@ -141,7 +141,7 @@ ptm_fused_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride, const
 // of only when two co-resident CTAs happen to be in different phases.  Under the table's write
 // stream a global read takes thousands of cycles, far more than eight fit warps can hide with
 // register prefetch, so the fit warps pull their frame bytes through a cp.async ring in shared
-// memory ([4 stages][64 frames][256 pixels], three chunks in flight, one barrier per chunk); the
+// memory ([2 stages][256 frames][256 pixels], the next chunk in flight, one barrier per chunk); the
 // camera table (n x 24 B) is loaded once per CTA.  Coefficients pass through a double-buffered smem
 // tile guarded by named barriers (full[b]: ids 2,3; empty[b]: ids 4,5); barrier 1 synchronises the
 // fit warps alone.
@@ -150,8 +150,12 @@ constexpr int WS_TABLE_WARPS = 16;
 constexpr int WS_TABLE_THREADS = 32 * WS_TABLE_WARPS;
 constexpr int WS_THREADS = WS_PIX + WS_TABLE_THREADS;          // 768: 8 fit warps + 16 table warps
 // register split (setmaxnreg, per warpgroup): 768 x 80 at launch = 256 x 112 (fit) + 512 x 64 (table)
-constexpr int WS_CHUNK = 64;                       // frames per ring stage
-constexpr int WS_STAGES = 4;
+#ifndef WS_CHUNK_FRAMES
+#define WS_CHUNK_FRAMES 256       /* measured: 64x4 7.02 ms, 128x3 6.95, 256x2 6.91 at 1024^2 x 500: fewer, larger */
+#define WS_RING_STAGES 2         /* read bursts disturb the table's write stream less                            */
+#endif
+constexpr int WS_CHUNK = WS_CHUNK_FRAMES;          // frames per ring stage
+constexpr int WS_STAGES = WS_RING_STAGES;
 constexpr int WS_DEPTH = WS_STAGES - 1;            // chunks in flight
 constexpr int WS_STAGE_BYTES = WS_CHUNK * WS_PIX;
 constexpr int WS_MAX_LIGHTS = 4096;                // camera table resident in smem (96 KB at the cap)
@@ -208,6 +212,7 @@ void release_tile_counters() {
     cudaSetDevice(cur);
 }
 
+constexpr size_t WS_SMEM_LIMIT = 227 * 1024 - 1024;      // dynamic smem the kernel may ask for (static part is < 1 KB)
 static size_t ws_smem_bytes(int n, int g) {
     return (size_t)WS_STAGES * WS_STAGE_BYTES + WS_COEF_BYTES + ((size_t)3 * n + g) * sizeof(double);
 }
@@ -439,7 +444,7 @@ extern "C" int rti_ptm_fit_table_frames(const uint8_t *d_frames, int64_t frame_s
     // The warp-specialised kernel needs 16-byte aligned frame rows (cp.async) and the camera table
     // resident in shared memory; anything else takes the phased kernel.
     static const char *variant = getenv("RTI_FUSED_KERNEL");       // "phased" forces the phased kernel (A/B runs)
-    const bool ws_ok = n <= WS_MAX_LIGHTS && frame_stride % 16 == 0 &&
+    const bool ws_ok = n <= WS_MAX_LIGHTS && ws_smem_bytes(n, g) <= WS_SMEM_LIMIT && frame_stride % 16 == 0 &&
                        (reinterpret_cast<uintptr_t>(d_frames) & 15) == 0 && !(variant && variant[0] == 'p');
     if (!ws_ok) {
         const size_t smem = (size_t)g * sizeof(double);
@@ -465,7 +470,7 @@ extern "C" int rti_ptm_fit_table_frames(const uint8_t *d_frames, int64_t frame_s
 #define RTI_WS_LAUNCH(V)                                                                                        \
     do {                                                                                                        \
         RTI_CUDA(cudaFuncSetAttribute(ptm_fused_ws_kernel<V>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
-                                      (int)ws_smem_bytes(WS_MAX_LIGHTS, 2048)));                                \
+                                      (int)WS_SMEM_LIMIT));                                \
         ptm_fused_ws_kernel<V><<<grid, WS_THREADS, smem, as_stream(stream)>>>(                                  \
             d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_axis, g, d_coef, plane_stride, d_table,  \
             image_stride, d_bad, counter);                                                                      \
