@@ -134,17 +134,18 @@ ptm_fused_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride, const
 
 
 // ---------------------------------------------------------------------------------------------
-// Warp-specialised persistent form.  One CTA of 512 threads per SM walks tiles of 256 pixels:
-//   warps 0-7  ("fit"):   thread = pixel, produce the coefficients of tile i+1
-//   warps 8-15 ("table"): stream the int32 table of tile i (same mapping as phase 2 above)
-// so the fp64/ALU-bound fit and the HBM-bound stores overlap inside every SM all the time instead
+// Warp-specialised persistent form.  One CTA of 768 threads per SM walks tiles of 256 pixels
+// claimed from an atomic counter:
+//   warps 0-7  ("fit"):   thread = pixel, produce the coefficients of the next tiles
+//   warps 8-23 ("table"): stream the int32 table of the current tile (lane = 4 pixels)
+// so the fp64/XU-bound fit and the HBM-bound stores overlap inside every SM all the time instead
 // of only when two co-resident CTAs happen to be in different phases.  Under the table's write
 // stream a global read takes thousands of cycles, far more than eight fit warps can hide with
 // register prefetch, so the fit warps pull their frame bytes through a cp.async ring in shared
 // memory ([2 stages][256 frames][256 pixels], the next chunk in flight, one barrier per chunk); the
-// camera table (n x 24 B) is loaded once per CTA.  Coefficients pass through a double-buffered smem
-// tile guarded by named barriers (full[b]: ids 2,3; empty[b]: ids 4,5); barrier 1 synchronises the
-// fit warps alone.
+// camera table (n x 24 B) is loaded once per CTA.  Coefficients pass through a three-deep smem
+// ring guarded by mbarriers (full[b] / empty[b], one arrival per warp); named barrier 1 synchronises
+// the fit warps alone.
 constexpr int WS_PIX = 256;
 constexpr int WS_TABLE_WARPS = 16;
 constexpr int WS_TABLE_THREADS = 32 * WS_TABLE_WARPS;
@@ -170,9 +171,6 @@ constexpr int WS_COEF_BYTES = WS_NBUF * 6 * WS_PIX * 8;
 
 __device__ __forceinline__ void bar_sync(int id, int count) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory");
-}
-__device__ __forceinline__ void bar_arrive(int id, int count) {
-    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory");
 }
 __device__ __forceinline__ void cp_async16_zfill(void *smem, const void *gmem, int src_bytes) {
     const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
