@@ -78,6 +78,16 @@ int rti_ptm_fit_frames(const uint8_t *d_frames, int64_t frame_stride, const doub
                        int n, int row0, int rows, int cols,
                        double *d_coef, int64_t plane_stride, int32_t *d_bad,
                        rti_stream_t stream);
+/* per-pixel validity masks (extension; the reference fits every pixel on all frames): a sample
+ * takes part in a pixel's fit only when its intensity lies in [lo, hi] (0 <= lo <= hi <= 255), i.e.
+ * the result equals _interpolate_PTM (analysis.py:263-298) called with the pixel's masked
+ * sub-arrays.  d_valid_count (int32 [n_pixels], may be NULL) receives the number of valid samples;
+ * pixels with fewer than 6 (the reference raises there, :296-298) or a singular system are counted
+ * in d_bad and get NaN coefficients. */
+int rti_ptm_fit_frames_masked(const uint8_t *d_frames, int64_t frame_stride, const double *d_cams,
+                              int n, int row0, int rows, int cols, int lo, int hi,
+                              double *d_coef, int64_t plane_stride, int32_t *d_valid_count,
+                              int32_t *d_bad, rti_stream_t stream);
 /* from materialised (lx, ly, intensity) arrays as rti_gather_soa /
  * compute_intensities produce them: one warp per pixel, shuffle reduction */
 int rti_ptm_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten,

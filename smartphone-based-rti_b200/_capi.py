@@ -50,6 +50,7 @@ SIGNATURES = {
     "rti_launch_count": (_l, [_i]),
     "rti_gather_soa": (_i, [_p, _l, _p, _i, _i, _i, _i, _p, _p, _p, _p]),
     "rti_ptm_fit_frames": (_i, [_p, _l, _p, _i, _i, _i, _i, _p, _l, _p, _p]),
+    "rti_ptm_fit_frames_masked": (_i, [_p, _l, _p, _i, _i, _i, _i, _i, _i, _p, _l, _p, _p, _p]),
     "rti_ptm_fit_soa": (_i, [_p, _p, _p, _l, _i, _p, _l, _p, _p]),
     "rti_ptm_fit_shared": (_i, [_p, _l, _p, _i, _l, _p, _l, _p]),
     "rti_lights_shared": (_i, [_p, _p, _l, _i, _p, _p]),

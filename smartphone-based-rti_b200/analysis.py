@@ -247,6 +247,35 @@ def _fit_ptm_from_stack(stack: FrameStack):
     return coef, bad
 
 
+def interpolate_ptm_masked(data, valid_range, first_only=False):
+    """PTM with per-pixel validity masks (extension): like
+    ``interpolate_intensities(data, interpolate_PTM=True)`` but a frame contributes to a pixel only
+    when its intensity there lies in ``valid_range = (lo, hi)`` (shadow / highlight rejection).  Equals
+    the reference's ``_interpolate_PTM`` called with each pixel's masked sub-arrays.  ``data``: the frame
+    records, a FrameStack, or the tuple compute_intensities returned.  Returns (result, valid_count)
+    with valid_count an int32 (rows, cols) device tensor; pixels with fewer than 6 valid samples raise
+    RtiSingularError (the reference fails in np.dot there, analysis.py:296-298)."""
+    torch = _torch()
+    lo, hi = int(valid_range[0]), int(valid_range[1])
+    range_val = 1 if first_only else _cst.ROI_DIAMETER
+    if isinstance(data, tuple) and len(data) == 3 and isinstance(data[0], DeviceArrayView):
+        stack = data[0]._soa.stack
+    elif isinstance(data, FrameStack):
+        stack = data
+    else:
+        if data is None or len(data) <= 0:
+            raise Exception("Error computing interpolation: results are empty or invalid")
+        stack = FrameStack(*_stack_frames(data, range_val, range_val))
+    coef = torch.empty((6, stack.n_pixels), dtype=torch.float64, device="cuda")
+    count = torch.empty((stack.rows, stack.cols), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_frames_masked", stack.d_frames.data_ptr(), stack.rows * stack.cols,
+               stack.d_cams.data_ptr(), stack.n, stack.row0, stack.rows, stack.cols, lo, hi,
+               coef.data_ptr(), stack.n_pixels, count.data_ptr(), bad.data_ptr(), _stream_ptr(torch))
+    _raise_if_bad(bad, "masked PTM")
+    return InterpolationResult("ptm", stack.rows, stack.cols, light_axis(), coef=coef, row0=stack.row0), count
+
+
 def _as_device_soa(data, range_val):
     """(lx, ly, inten) as device (P, N) tensors restricted to [range_val, range_val]."""
     torch = _torch()

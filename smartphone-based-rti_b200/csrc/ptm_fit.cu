@@ -15,11 +15,17 @@ constexpr int FIT_THREADS = 128;
 constexpr int FIT_CAM_CHUNK = 512;      // frames of camera data resident in smem at a time
 constexpr int FIT_UNROLL = 4;           // independent byte loads in flight per thread
 
+// MASKED: per-pixel validity masks.  A sample takes part in pixel p's fit only when its intensity lies in
+// [lo, hi] (shadow / highlight rejection), so every pixel has its own sample set; the oracle is the
+// reference's _interpolate_PTM called with the pixel's masked sub-arrays.  Rejected
+// samples enter with a zero design row and zero intensity, the sample count becomes per pixel, and a
+// pixel with fewer than 6 valid samples is flagged like a singular one (the reference raises, :296-298).
+template <bool MASKED>
 __global__ void __launch_bounds__(FIT_THREADS)
 ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
                       const double *__restrict__ cams, int n, int row0, int cols,
                       int64_t n_pixels, double *__restrict__ coef, int64_t plane_stride,
-                      int32_t *__restrict__ bad) {
+                      int32_t *__restrict__ bad, int lo, int hi, int32_t *__restrict__ valid_count) {
     __shared__ double s_cam[FIT_CAM_CHUNK][3];
     const int64_t p = (int64_t)blockIdx.x * FIT_THREADS + threadIdx.x;
     const bool active = p < n_pixels;
@@ -31,6 +37,17 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
 
     NormalEq ne;
     ne.clear();
+    int count = MASKED ? 0 : n;
+    auto add_sample = [&](float lu, float lv, unsigned v) {
+        if (MASKED) {
+            const bool valid = (int)v >= lo && (int)v <= hi;
+            count += valid ? 1 : 0;
+            lu = valid ? lu : 0.0f;
+            lv = valid ? lv : 0.0f;
+            v = valid ? v : 0u;
+        }
+        ne.add(lu, lv, u8_to_double(v));
+    };
     for (int f0 = 0; f0 < n; f0 += FIT_CAM_CHUNK) {
         const int fc = min(FIT_CAM_CHUNK, n - f0);
         __syncthreads();
@@ -50,21 +67,27 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
             for (int j = 0; j < FIT_UNROLL; ++j) {
                 float lu, lv;
                 light_vector(s_cam[i + j][0], s_cam[i + j][1], s_cam[i + j][2], xd, yd, lu, lv);
-                ne.add(lu, lv, u8_to_double(v[j]));
+                add_sample(lu, lv, v[j]);
             }
         }
         for (; i < fc; ++i) {
             const uint8_t v = __ldg(src + (int64_t)(f0 + i) * frame_stride);
             float lu, lv;
             light_vector(s_cam[i][0], s_cam[i][1], s_cam[i][2], xd, yd, lu, lv);
-            ne.add(lu, lv, u8_to_double(v));
+            add_sample(lu, lv, v);
         }
     }
     double a[6];
-    const bool ok = solve_normal_eq(ne, (double)n, a);
+    bool ok = solve_normal_eq(ne, (double)count, a);
+    if (MASKED && count < 6) {
+        ok = false;
+#pragma unroll
+        for (int k = 0; k < 6; ++k) a[k] = __longlong_as_double(0x7FF8000000000000LL);
+    }
     if (active) {
 #pragma unroll
         for (int k = 0; k < 6; ++k) coef[k * plane_stride + p] = a[k];
+        if (MASKED && valid_count != nullptr) valid_count[p] = count;
         if (!ok && bad != nullptr) atomicAdd(bad, 1);
     }
 }
@@ -276,9 +299,29 @@ extern "C" int rti_ptm_fit_frames(const uint8_t *d_frames, int64_t frame_stride,
     RTI_REQUIRE(plane_stride >= n_pixels, "rti_ptm_fit_frames: plane_stride < pixels");
     RTI_REQUIRE(frame_stride >= n_pixels, "rti_ptm_fit_frames: frame_stride < slab pixels");
     const int64_t blocks = (n_pixels + FIT_THREADS - 1) / FIT_THREADS;
-    ptm_fit_frames_kernel<<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
-        d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad);
+    ptm_fit_frames_kernel<false><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
+        d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, 0, 255, nullptr);
     RTI_LAUNCHED("ptm_fit_frames_kernel");
+    return RTI_OK;
+}
+
+extern "C" int rti_ptm_fit_frames_masked(const uint8_t *d_frames, int64_t frame_stride, const double *d_cams,
+                                         int n, int row0, int rows, int cols, int lo, int hi, double *d_coef,
+                                         int64_t plane_stride, int32_t *d_valid_count, int32_t *d_bad,
+                                         rti_stream_t stream) {
+    RTI_REQUIRE(d_frames && d_cams && d_coef, "rti_ptm_fit_frames_masked: NULL pointer");
+    RTI_REQUIRE(rows > 0 && cols > 0 && row0 >= 0, "rti_ptm_fit_frames_masked: bad slab %d+%d x %d", row0, rows, cols);
+    RTI_REQUIRE(lo >= 0 && hi <= 255 && lo <= hi, "rti_ptm_fit_frames_masked: bad intensity range [%d, %d]", lo, hi);
+    if (n < 6) {
+        set_error("rti_ptm_fit_frames_masked: PTM needs >= 6 light samples, got %d", n);
+        return n <= 0 ? RTI_ERR_ARG : RTI_ERR_TOO_FEW;
+    }
+    const int64_t n_pixels = (int64_t)rows * cols;
+    RTI_REQUIRE(plane_stride >= n_pixels && frame_stride >= n_pixels, "rti_ptm_fit_frames_masked: stride < slab pixels");
+    const int64_t blocks = (n_pixels + FIT_THREADS - 1) / FIT_THREADS;
+    ptm_fit_frames_kernel<true><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
+        d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, lo, hi, d_valid_count);
+    RTI_LAUNCHED("ptm_fit_frames_kernel<masked>");
     return RTI_OK;
 }
 

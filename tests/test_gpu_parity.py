@@ -705,3 +705,63 @@ def test_fused_ws_kernel_stays_inside_its_buffers(torch_cuda):
     assert np.abs(cv[:, :p] - ref).max() <= PTM_COEF_RTOL * np.abs(ref).max()
     want = orc.table_from_grids(orc.ptm_grid(ref.T.reshape(rows, cols, 6), ax)).reshape(g * g, p)
     assert np.array_equal(tv[:, :p], want)
+
+
+# ------------------------------------------------------------------ per-pixel validity masks
+def test_ptm_masked_fit_equals_reference_on_masked_subarrays(torch_cuda):
+    """Extension named by the north star (per-pixel validity masks): the oracle is the reference's
+    per-pixel fit called with only the samples whose intensity lies in [lo, hi]."""
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    rows, cols, n, lo, hi = 9, 21, 60, 40, 215
+    frames, cams = synthetic.lambertian_stack(rows, cols, n, seed=17, noise=25.0)
+    p = rows * cols
+    d_f, d_c = dev(torch, frames), dev(torch, cams)
+    coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+    count = torch.empty(p, dtype=torch.int32, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_frames_masked", d_f.data_ptr(), p, d_c.data_ptr(), n, 0, rows, cols, lo, hi,
+               coef.data_ptr(), p, count.data_ptr(), bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    lx, ly, inten = orc.gather_soa(frames, cams)
+    got = coef.cpu().numpy().reshape(6, rows, cols)
+    cnt = count.cpu().numpy().reshape(rows, cols)
+    n_bad = 0
+    checked = 0
+    for y in range(rows):
+        for x in range(cols):
+            m = (inten[y, x] >= lo) & (inten[y, x] <= hi)
+            assert cnt[y, x] == m.sum()
+            if m.sum() < 6:
+                n_bad += 1
+                assert np.all(np.isnan(got[:, y, x]))
+                continue
+            ref = orc.ptm_fit(lx[y, x][m], ly[y, x][m], inten[y, x][m])
+            if np.linalg.cond(orc.ptm_design(lx[y, x][m], ly[y, x][m])) < 1e6:
+                assert np.abs(got[:, y, x] - ref).max() <= 1e-8 * np.abs(ref).max()
+                checked += 1
+    assert checked > p // 2 and not (cnt == n).all()          # masks really differ between pixels
+    assert bad.item() >= n_bad
+    # a full range reproduces the unmasked fit bit for bit
+    coef_all, bad_all = gpu_fit_frames(torch, frames, cams)
+    _capi.call("rti_ptm_fit_frames_masked", d_f.data_ptr(), p, d_c.data_ptr(), n, 0, rows, cols, 0, 255,
+               coef.data_ptr(), p, count.data_ptr(), bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert torch.equal(coef, coef_all) and (count == n).all()
+
+
+def test_ptm_masked_call_surface(torch_cuda, monkeypatch):
+    import rti_b200
+    from rti_b200 import analysis, synthetic
+    r, n = 8, 40
+    frames, cams = synthetic.lambertian_stack(r, r, n, seed=4, noise=20.0)
+    monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", r)
+    res, count = analysis.interpolate_ptm_masked(synthetic.as_records(frames, cams), (10, 245))
+    assert res.mode == "ptm" and tuple(count.shape) == (r, r)
+    lx, ly, inten = orc.gather_soa(frames, cams)
+    m = (inten[3, 5] >= 10) & (inten[3, 5] <= 245)
+    ref = orc.ptm_fit(lx[3, 5][m], ly[3, 5][m], inten[3, 5][m])
+    got = res.coefficients()[:, 3, 5]
+    assert np.abs(got - ref).max() <= 1e-8 * np.abs(ref).max()
+    with pytest.raises(rti_b200.RtiSingularError):
+        analysis.interpolate_ptm_masked(synthetic.as_records(frames, cams), (254, 255))   # almost nothing valid
