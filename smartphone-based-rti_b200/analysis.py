@@ -643,6 +643,9 @@ def read_from_file(filename, compressed=True):
     if compressed:
         from . import ingest
         return ingest.read_pbz2(filename)        # same object, bzip2 blocks decoded in parallel
+    table = table_io.load_table(filename)        # a result table written by this package: mapped, not read
+    if table is not None:
+        return table
     with open(filename, "rb") as f:
         return pickle.load(f)
 
@@ -743,9 +746,9 @@ def install(analysis_module, constants_module=None, fast_writer=True, fast_reade
         original_reader = ut.read_from_file
 
         def read_from_file_fast(filename, compressed=True):
-            if not compressed:
-                return original_reader(filename, compressed=compressed)
-            return read_from_file(filename, compressed=True)
+            # compressed: parallel bzip2 blocks; uncompressed (interactive_relighting.py:95): a table
+            # written by this package is memory-mapped copy-on-write, anything else is unpickled as before
+            return read_from_file(filename, compressed=compressed)
 
         read_from_file_fast._rti_b200 = True
         read_from_file_fast._original = original_reader

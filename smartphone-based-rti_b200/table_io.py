@@ -153,3 +153,90 @@ def dumps_table(table) -> bytes:
     buf = io.BytesIO()
     dump_table(table, buf)
     return buf.getvalue()
+
+
+def load_table(path):
+    """Memory-map a result pickle written by TableStreamWriter / dump_table and return the same object
+    graph ``pickle.load`` gives -- list[G_v] of list[G_u] of WRITABLE int32 (rows, cols) ndarrays --
+    without reading the file: every image is a view into one copy-on-write mapping (``mmap.ACCESS_COPY``),
+    so pages are read when an image is first touched and the relighter's in-place clamp
+    (interactive_relighting.py:35-36) stays private to the process.  Returns None when the file does
+    not have exactly this writer's byte layout (the caller then uses ``pickle.load``)."""
+    import mmap
+    import os
+    size = os.path.getsize(path)
+    with open(path, "rb") as f:
+        head = f.read(4096)
+        opener = pickle.PROTO + bytes([_PROTO]) + pickle.EMPTY_LIST + pickle.MARK + pickle.EMPTY_LIST + pickle.MARK
+        if not head.startswith(opener):
+            return None
+        # the first image's prefix ends with BINBYTES8 + length; recover shape and dtype by unpickling a
+        # one-image file made of the first image only
+        k = head.find(b"\x8e", len(opener))
+        while k >= 0:
+            nbytes = struct.unpack("<Q", head[k + 1:k + 9])[0] if k + 9 <= len(head) else 0
+            if 0 < nbytes <= size:
+                break
+            k = head.find(b"\x8e", k + 1)
+        if k < 0:
+            return None
+        prefix = head[len(opener):k + 9]
+        f.seek(len(opener) + len(prefix) + nbytes)
+        tail = f.read(512)
+        try:
+            probe_dtype, probe_shape, suffix = _probe_image(prefix, tail, nbytes)
+        except Exception:
+            return None
+        if probe_dtype != np.dtype(np.int32) or len(probe_shape) != 2:
+            return None
+        per_image = len(prefix) + nbytes + len(suffix)
+        row_open = pickle.EMPTY_LIST + pickle.MARK
+        row_close = pickle.APPENDS
+        closer = pickle.APPENDS + pickle.STOP
+        # size = 3 + 1 + gv * (2 + gu * per_image + 1) + 2  with gv, gu unknown: find gu from the first row
+        mm = mmap.mmap(f.fileno(), 0, access=mmap.ACCESS_COPY)
+    body0 = len(pickle.PROTO) + 1 + 2                       # PROTO n, EMPTY_LIST, MARK
+    gu = 0
+    pos = body0 + len(row_open)
+    while mm[pos:pos + len(prefix)] == prefix:
+        pos += per_image
+        gu += 1
+        if pos >= size:
+            return None
+    if gu == 0 or mm[pos:pos + 1] != row_close:
+        return None
+    row_bytes = len(row_open) + gu * per_image + len(row_close)
+    gv, rem = divmod(size - body0 - len(closer), row_bytes)
+    if rem != 0 or gv <= 0 or mm[size - len(closer):size] != closer:
+        return None
+    whole = np.frombuffer(mm, dtype=np.uint8)               # writable: private copy-on-write pages
+    out = []
+    for v in range(gv):
+        base = body0 + v * row_bytes
+        if mm[base:base + len(row_open)] != row_open or mm[base + row_bytes - 1:base + row_bytes] != row_close:
+            return None
+        row = []
+        for u in range(gu):
+            at = base + len(row_open) + u * per_image
+            if mm[at:at + len(prefix)] != prefix or \
+                    mm[at + len(prefix) + nbytes:at + per_image] != suffix:
+                return None
+            img = whole[at + len(prefix):at + len(prefix) + nbytes].view(np.int32).reshape(probe_shape)
+            row.append(img)
+        out.append(row)
+    return out
+
+
+def _probe_image(prefix, tail, nbytes):
+    """dtype, shape and suffix bytes of the images of a stream: the suffix is this writer's template
+    suffix for the (shape, dtype) that the prefix announces; found by trying the template of every
+    2-D int32 shape with nbytes bytes whose prefix matches."""
+    n = nbytes // 4
+    for rows in range(1, n + 1):
+        if n % rows:
+            continue
+        cols = n // rows
+        p, s = _array_template((rows, cols), np.int32)
+        if p == prefix and tail.startswith(s):
+            return np.dtype(np.int32), (rows, cols), s
+    raise ValueError("not a TableStreamWriter image")

@@ -166,3 +166,42 @@ def test_write_on_file_uses_streaming_writer_and_reference_reader_loads_it(tmp_p
     assert rti_b200.read_from_file(str(tmp_path / "other"), compressed=False) == {"a": 1}
     rti_b200.write_on_file(images, str(tmp_path / "z"), compressed=True)
     assert np.array_equal(rti_b200.read_from_file(str(tmp_path / "z"))[1][2], table[1, 2])
+
+
+def test_load_table_maps_the_result_pickle(tmp_path):
+    """SURVEY 8(f1) loader: interactive_relighting.py:95 un-pickles the 6.4 GB table; a table written by
+    this package is memory-mapped instead (copy-on-write), same object graph, in-place clamp allowed."""
+    import pickle
+    import rti_b200
+    from rti_b200 import table_io
+    rng = np.random.default_rng(5)
+    table = rng.integers(-300, 600, (4, 6, 5, 8)).astype(np.int32)
+    path = str(tmp_path / "interpolation_results_x")
+    with open(path + ".pickle", "wb") as f:
+        table_io.dump_table(table, f)
+    got = rti_b200.read_from_file(path, compressed=False)
+    ref = pickle.load(open(path + ".pickle", "rb"))
+    assert isinstance(got, list) and len(got) == 4 and all(isinstance(r, list) and len(r) == 6 for r in got)
+    for v in range(4):
+        for u in range(6):
+            assert got[v][u].dtype == np.int32 and got[v][u].shape == (5, 8) and got[v][u].flags.writeable
+            assert np.array_equal(got[v][u], ref[v][u])
+    assert got[0][0].base is not None and table_io.load_table(path + ".pickle") is not None
+    values = got[1][2]
+    values[values > 255] = 255
+    values[values <= 0] = 0                                   # private pages: the file is unchanged
+    assert np.array_equal(pickle.load(open(path + ".pickle", "rb"))[1][2], table[1, 2])
+    # files of any other shape fall back to pickle.load
+    other = str(tmp_path / "other")
+    with open(other + ".pickle", "wb") as f:
+        pickle.dump([[table[v, u] for u in range(6)] for v in range(4)], f)
+    assert table_io.load_table(other + ".pickle") is None
+    back = rti_b200.read_from_file(other, compressed=False)
+    assert np.array_equal(np.array(back), table)
+    with open(other + ".pickle", "wb") as f:
+        pickle.dump({"not": "a table"}, f)
+    assert rti_b200.read_from_file(other, compressed=False) == {"not": "a table"}
+    # a truncated table is not mapped
+    raw = open(path + ".pickle", "rb").read()
+    open(path + ".pickle", "wb").write(raw[:-7])
+    assert table_io.load_table(path + ".pickle") is None

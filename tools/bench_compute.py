@@ -101,6 +101,11 @@ def main():
             with open(path, "rb") as f:
                 back = pickle.load(f)
             load_s = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            mapped = analysis.read_from_file("assets/interpolation_results_synth", compressed=False)   # mmap loader
+            mapped_ok = bool(np.array_equal(mapped[50][50], back[50][50]) and mapped[50][50].flags.writeable)
+            map_s = time.perf_counter() - t0
+            del mapped
             # the same table again through the separate public functions (the install() route)
             t0 = time.perf_counter()
             images = analysis.prepare_images_data(analysis.interpolate_intensities(
@@ -114,7 +119,7 @@ def main():
             ok = (len(back) == 100 and len(back[0]) == 100 and back[3][7].dtype == np.int32
                   and back[3][7].shape == (r, r) and back[3][7].flags.writeable
                   and all(np.array_equal(back[v][u], images[v][u]) for v, u in ((0, 0), (3, 7), (50, 50), (99, 99))))
-            out[mode] = {"total_s": total, "stages_s": st.times, "result_bytes": size, "reload_s": load_s,
+            out[mode] = {"total_s": total, "stages_s": st.times, "result_bytes": size, "reload_s": load_s, "mapped_load_s": map_s, "mapped_ok": mapped_ok,
                          "separate_calls_s": separate_s, "install_route_write_s": install_write_s,
                          "install_route_same_size": bool(same_file), "result_file_ok": bool(ok),
                          "mpixel_lights_per_s_wall": r * r * n / total / 1e6}
