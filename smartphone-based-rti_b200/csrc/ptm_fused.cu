@@ -157,10 +157,16 @@ constexpr int WS_THREADS = WS_PIX + WS_TABLE_THREADS;          // 768: 8 fit war
 #endif
 constexpr int WS_CHUNK = WS_CHUNK_FRAMES;          // frames per ring stage
 constexpr int WS_STAGES = WS_RING_STAGES;
+#ifndef WS_UNROLL
+#define WS_UNROLL 4
+#endif
 constexpr int WS_DEPTH = WS_STAGES - 1;            // chunks in flight
 constexpr int WS_STAGE_BYTES = WS_CHUNK * WS_PIX;
 constexpr int WS_MAX_LIGHTS = 4096;                // camera table resident in smem (96 KB at the cap)
-constexpr int WS_NBUF = 3;                         // coefficient tiles between the fit and the table warps
+#ifndef WS_COEF_BUFS
+#define WS_COEF_BUFS 3
+#endif
+constexpr int WS_NBUF = WS_COEF_BUFS;              // coefficient tiles between the fit and the table warps
 constexpr int WS_COEF_BYTES = WS_NBUF * 6 * WS_PIX * 8;
 #ifndef WS_FIT_REGS
 #define WS_FIT_REGS 112
@@ -315,9 +321,9 @@ ptm_fused_ws_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride, co
                 const uint8_t *src = s_ring + cstage * WS_STAGE_BYTES + t;
                 const double *cam = s_cam + 3 * f0;
                 int i = 0;
-                for (; i + FU_UNROLL <= fc; i += FU_UNROLL) {
+                for (; i + WS_UNROLL <= fc; i += WS_UNROLL) {
 #pragma unroll
-                    for (int k = 0; k < FU_UNROLL; ++k) {
+                    for (int k = 0; k < WS_UNROLL; ++k) {
                         float lu, lv;
                         light_vector(cam[3 * (i + k)], cam[3 * (i + k) + 1], cam[3 * (i + k) + 2], xd, yd, lu, lv);
                         ne.add(lu, lv, u8_to_double(src[(i + k) * WS_PIX]));
