@@ -29,9 +29,16 @@ constexpr int G_THREADS = 256;
 constexpr int G_WARPS = G_THREADS / 32;
 constexpr int G_QPW = 32 / G_WARPS;                  // frame quads per warp and chunk (4)
 constexpr size_t G_SMEM = 3 * G_PIX * 32 * 16 + G_FRAMES * 3 * sizeof(double);
+// ASYNC: the frame bytes of a chunk ([128 frames][32 pixels] = 4 KB) come through a three-stage cp.async
+// ring, two chunks ahead, instead of one chunk ahead in registers: under this kernel's own write
+// stream a global read takes thousands of cycles and ncu showed half of the warps waiting on the
+// register prefetch (long scoreboard 4.1 warps per issue).  Needs 16-byte aligned 32-pixel runs.
+constexpr int G_STAGES = 3;
+constexpr size_t G_RING = (size_t)G_STAGES * G_FRAMES * G_PIX;
+constexpr size_t G_SMEM_ASYNC = G_SMEM + G_RING;
 
-template <bool VEC>
-__global__ void __launch_bounds__(G_THREADS, 4)
+template <bool VEC, bool ASYNC>
+__global__ void __launch_bounds__(G_THREADS, ASYNC ? 3 : 4)
 gather_soa_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
                   const double *__restrict__ cams, int n, int row0, int cols, int64_t n_pixels,
                   float *__restrict__ lx, float *__restrict__ ly, int32_t *__restrict__ inten) {
@@ -41,6 +48,7 @@ gather_soa_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
     int4 *s_in = reinterpret_cast<int4 *>(s_ly + G_PIX * 32);
     double (*s_cam)[3] = reinterpret_cast<double (*)[3]>(s_in + G_PIX * 32);
     double *s_camflat = &s_cam[0][0];
+    uint8_t *s_ring = reinterpret_cast<uint8_t *>(s_camflat + 3 * G_FRAMES);   // ASYNC only: [stage][frame][pixel]
 
     const int64_t pix0 = (int64_t)blockIdx.x * G_PIX;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -78,19 +86,51 @@ gather_soa_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
         }
     };
 
+    // ASYNC: thread t copies half h = t & 1 of frame f0 + (t >> 1)'s 32-byte pixel run
+    const int valid_bytes = (int)min((int64_t)G_PIX, n_pixels - pix0);
+    auto issue = [&](int f0, int stage) {
+        const int f = f0 + (threadIdx.x >> 1), h = threadIdx.x & 1;
+        const int nb = min(16, valid_bytes - 16 * h);
+        if (f < n && nb > 0) {
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(s_ring + ((size_t)stage * G_FRAMES + (threadIdx.x >> 1)) * G_PIX + 16 * h);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst),
+                         "l"(frames + (int64_t)f * frame_stride + pix0 + 16 * h), "r"(nb) : "memory");
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+
     uint8_t cur[G_QPW][4], nxt[G_QPW][4];
     double ccam[2];
     cam_fetch(0, ccam);
-    fetch(0, cur);
+    if (ASYNC) {
+        issue(0, 0);
+        issue(G_FRAMES, 1);
+    } else {
+        fetch(0, cur);
+    }
     cam_park(ccam);
+    int stage = 0;
     for (int f0 = 0; f0 < n; f0 += G_FRAMES) {
         const int fc = min(G_FRAMES, n - f0);
         const bool has_next = f0 + G_FRAMES < n;
         if (has_next) {
-            fetch(f0 + G_FRAMES, nxt);
+            if (!ASYNC) fetch(f0 + G_FRAMES, nxt);
             cam_fetch(f0 + G_FRAMES, ccam);
         }
+        if (ASYNC) asm volatile("cp.async.wait_group 1;\n" ::: "memory");     // this chunk's bytes have landed
         __syncthreads();        // this chunk's camera table is parked; the previous phase 2 has drained
+        if (ASYNC) {
+            issue(f0 + 2 * G_FRAMES, stage == 0 ? 2 : stage - 1);              // the stage of the previous chunk
+            const uint8_t *bytes = s_ring + (size_t)stage * G_FRAMES * G_PIX + lane;
+#pragma unroll
+            for (int i = 0; i < G_QPW; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int fl = (warp + i * G_WARPS) * 4 + j;
+                    cur[i][j] = (fl < fc && lane < valid_bytes) ? bytes[fl * G_PIX] : (uint8_t)0;
+                }
+            stage = stage == 2 ? 0 : stage + 1;
+        }
         // ---- phase 1: light vectors in fp64, parked as float4/int4 chunks
 #pragma unroll
         for (int i = 0; i < G_QPW; ++i) {
@@ -142,11 +182,14 @@ gather_soa_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
                 }
             }
         }
+        if (!ASYNC) {
 #pragma unroll
-        for (int i = 0; i < G_QPW; ++i)
+            for (int i = 0; i < G_QPW; ++i)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) cur[i][j] = nxt[i][j];
+                for (int j = 0; j < 4; ++j) cur[i][j] = nxt[i][j];
+        }
     }
+    if (ASYNC) asm volatile("cp.async.wait_group 0;\n" ::: "memory");
 }
 
 // ---- TMA-store variant (n % 4 == 0, 16-byte aligned outputs) ---------------------------------
@@ -279,8 +322,13 @@ extern "C" int rti_gather_soa(const uint8_t *d_frames, int64_t frame_stride, con
                      ((reinterpret_cast<uintptr_t>(d_ly) & 15) == 0) &&
                      ((reinterpret_cast<uintptr_t>(d_inten) & 15) == 0);
     // per device and idempotent; cheap enough to repeat on every call
-    RTI_CUDA(cudaFuncSetAttribute(gather_soa_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM));
-    RTI_CUDA(cudaFuncSetAttribute(gather_soa_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM));
+    RTI_CUDA(cudaFuncSetAttribute(gather_soa_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM));
+    RTI_CUDA(cudaFuncSetAttribute(gather_soa_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM));
+    RTI_CUDA(cudaFuncSetAttribute(gather_soa_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_ASYNC));
+    RTI_CUDA(cudaFuncSetAttribute(gather_soa_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_ASYNC));
+    const char *env_async = getenv("RTI_GATHER_ASYNC");
+    const bool async = (env_async == nullptr || env_async[0] != '0') && frame_stride % 16 == 0 &&
+                       (reinterpret_cast<uintptr_t>(d_frames) & 15) == 0;
     const char *env_tma = getenv("RTI_GATHER_TMA");
     const bool want_tma = env_tma == nullptr || env_tma[0] != '0';
     // TMA-store kernel when every pixel row starts on a 32-byte sector (n % 8 == 0): 5.0 TB/s against 4.2 for
@@ -299,11 +347,17 @@ extern "C" int rti_gather_soa(const uint8_t *d_frames, int64_t frame_stride, con
         RTI_CUDA(cudaFuncSetAttribute(gather_soa_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)T_SMEM));
         gather_soa_tma_kernel<<<(unsigned)bx, T_THREADS, T_SMEM, as_stream(stream)>>>(
             map_lx, map_ly, map_in, d_frames, frame_stride, d_cams, n, row0, cols, n_pixels);
-    } else if (vec)
-        gather_soa_kernel<true><<<(unsigned)bx, G_THREADS, G_SMEM, as_stream(stream)>>>(
+    } else if (vec && async)
+        gather_soa_kernel<true, true><<<(unsigned)bx, G_THREADS, G_SMEM_ASYNC, as_stream(stream)>>>(
+            d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_lx, d_ly, d_inten);
+    else if (vec)
+        gather_soa_kernel<true, false><<<(unsigned)bx, G_THREADS, G_SMEM, as_stream(stream)>>>(
+            d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_lx, d_ly, d_inten);
+    else if (async)
+        gather_soa_kernel<false, true><<<(unsigned)bx, G_THREADS, G_SMEM_ASYNC, as_stream(stream)>>>(
             d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_lx, d_ly, d_inten);
     else
-        gather_soa_kernel<false><<<(unsigned)bx, G_THREADS, G_SMEM, as_stream(stream)>>>(
+        gather_soa_kernel<false, false><<<(unsigned)bx, G_THREADS, G_SMEM, as_stream(stream)>>>(
             d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_lx, d_ly, d_inten);
     RTI_LAUNCHED("gather_soa_kernel");
     return RTI_OK;
