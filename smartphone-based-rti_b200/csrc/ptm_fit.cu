@@ -20,13 +20,19 @@ constexpr int FIT_UNROLL = 4;           // independent byte loads in flight per 
 // reference's _interpolate_PTM called with the pixel's masked sub-arrays.  Rejected
 // samples enter with a zero design row and zero intensity, the sample count becomes per pixel, and a
 // pixel with fewer than 6 valid samples is flagged like a singular one (the reference raises, :296-298).
-template <bool MASKED>
+// ASYNC: the CTA's frame bytes ([64 frames][128 pixels] per chunk) come through a three-stage cp.async
+// ring two chunks ahead instead of four byte loads per thread (needs 16-byte aligned frame rows).
+constexpr int FIT_CHUNK = 64;
+constexpr int FIT_STAGES = 3;
+
+template <bool MASKED, bool ASYNC>
 __global__ void __launch_bounds__(FIT_THREADS)
 ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
                       const double *__restrict__ cams, int n, int row0, int cols,
                       int64_t n_pixels, double *__restrict__ coef, int64_t plane_stride,
                       int32_t *__restrict__ bad, int lo, int hi, int32_t *__restrict__ valid_count) {
     __shared__ double s_cam[FIT_CAM_CHUNK][3];
+    __shared__ __align__(16) uint8_t s_ring[ASYNC ? FIT_STAGES * FIT_CHUNK * FIT_THREADS : 16];
     const int64_t p = (int64_t)blockIdx.x * FIT_THREADS + threadIdx.x;
     const bool active = p < n_pixels;
     const int64_t pc = active ? p : n_pixels - 1;           // clamp: tail threads redo the last pixel
@@ -48,6 +54,29 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
         }
         ne.add(lu, lv, u8_to_double(v));
     };
+    // ASYNC: chunk c = frames [64 c, 64 c + 64) goes to ring stage c % 3; 4 x 16 bytes per thread
+    const int64_t pbase = (int64_t)blockIdx.x * FIT_THREADS;
+    auto issue = [&](int c) {
+        const int f0 = c * FIT_CHUNK;
+#pragma unroll
+        for (int r = 0; r < FIT_CHUNK * (FIT_THREADS / 16) / FIT_THREADS; ++r) {
+            const int piece = threadIdx.x + r * FIT_THREADS;
+            const int f = piece >> 3, seg = piece & 7;
+            const int64_t left = n_pixels - (pbase + seg * 16);
+            if (f0 + f < n && left > 0) {
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(
+                    s_ring + ((c % FIT_STAGES) * FIT_CHUNK + f) * FIT_THREADS + seg * 16);
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst),
+                             "l"(frames + (int64_t)(f0 + f) * frame_stride + pbase + seg * 16),
+                             "r"(left >= 16 ? 16 : (int)left) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    if (ASYNC) {
+        issue(0);
+        issue(1);
+    }
     for (int f0 = 0; f0 < n; f0 += FIT_CAM_CHUNK) {
         const int fc = min(FIT_CAM_CHUNK, n - f0);
         __syncthreads();
@@ -58,6 +87,31 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
             s_cam[i][2] = cz * cz;
         }
         __syncthreads();
+        if (ASYNC) {
+            for (int i0 = 0; i0 < fc; i0 += FIT_CHUNK) {
+                const int c = (f0 + i0) / FIT_CHUNK;
+                asm volatile("cp.async.wait_group 1;\n" ::: "memory");
+                __syncthreads();                  // chunk c has landed for everyone; chunk c-1's stage is free
+                issue(c + 2);
+                const uint8_t *bytes = s_ring + (c % FIT_STAGES) * FIT_CHUNK * FIT_THREADS + threadIdx.x;
+                const int kc = min(FIT_CHUNK, fc - i0);
+                int k = 0;
+                for (; k + FIT_UNROLL <= kc; k += FIT_UNROLL) {
+#pragma unroll
+                    for (int j = 0; j < FIT_UNROLL; ++j) {
+                        float lu, lv;
+                        light_vector(s_cam[i0 + k + j][0], s_cam[i0 + k + j][1], s_cam[i0 + k + j][2], xd, yd, lu, lv);
+                        add_sample(lu, lv, bytes[(k + j) * FIT_THREADS]);
+                    }
+                }
+                for (; k < kc; ++k) {
+                    float lu, lv;
+                    light_vector(s_cam[i0 + k][0], s_cam[i0 + k][1], s_cam[i0 + k][2], xd, yd, lu, lv);
+                    add_sample(lu, lv, bytes[k * FIT_THREADS]);
+                }
+            }
+            continue;
+        }
         int i = 0;
         for (; i + FIT_UNROLL <= fc; i += FIT_UNROLL) {
             uint8_t v[FIT_UNROLL];
@@ -77,6 +131,7 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
             add_sample(lu, lv, v);
         }
     }
+    if (ASYNC) asm volatile("cp.async.wait_group 0;\n" ::: "memory");
     double a[6];
     bool ok = solve_normal_eq(ne, (double)count, a);
     if (MASKED && count < 6) {
@@ -299,8 +354,12 @@ extern "C" int rti_ptm_fit_frames(const uint8_t *d_frames, int64_t frame_stride,
     RTI_REQUIRE(plane_stride >= n_pixels, "rti_ptm_fit_frames: plane_stride < pixels");
     RTI_REQUIRE(frame_stride >= n_pixels, "rti_ptm_fit_frames: frame_stride < slab pixels");
     const int64_t blocks = (n_pixels + FIT_THREADS - 1) / FIT_THREADS;
-    ptm_fit_frames_kernel<false><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
-        d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, 0, 255, nullptr);
+    if (frame_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(d_frames) & 15) == 0)
+        ptm_fit_frames_kernel<false, true><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
+            d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, 0, 255, nullptr);
+    else
+        ptm_fit_frames_kernel<false, false><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
+            d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, 0, 255, nullptr);
     RTI_LAUNCHED("ptm_fit_frames_kernel");
     return RTI_OK;
 }
@@ -319,8 +378,12 @@ extern "C" int rti_ptm_fit_frames_masked(const uint8_t *d_frames, int64_t frame_
     const int64_t n_pixels = (int64_t)rows * cols;
     RTI_REQUIRE(plane_stride >= n_pixels && frame_stride >= n_pixels, "rti_ptm_fit_frames_masked: stride < slab pixels");
     const int64_t blocks = (n_pixels + FIT_THREADS - 1) / FIT_THREADS;
-    ptm_fit_frames_kernel<true><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
-        d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, lo, hi, d_valid_count);
+    if (frame_stride % 16 == 0 && (reinterpret_cast<uintptr_t>(d_frames) & 15) == 0)
+        ptm_fit_frames_kernel<true, true><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
+            d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, lo, hi, d_valid_count);
+    else
+        ptm_fit_frames_kernel<true, false><<<(unsigned)blocks, FIT_THREADS, 0, as_stream(stream)>>>(
+            d_frames, frame_stride, d_cams, n, row0, cols, n_pixels, d_coef, plane_stride, d_bad, lo, hi, d_valid_count);
     RTI_LAUNCHED("ptm_fit_frames_kernel<masked>");
     return RTI_OK;
 }
