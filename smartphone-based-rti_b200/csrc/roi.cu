@@ -11,183 +11,215 @@
 //   h = (h * hdiv[diff] + 2^11) >> 12 (arithmetic shift), h += 180 if h < 0,
 //                                                   hdiv[i] = rint(180 * 4096 / (6 i))
 // The op is a byte stream: 3 B read + 1 B (V) or 3 B (HSV) written per ROI pixel, HBM-bound.
-// A work item is a run of 1024 pixels of four ROI rows: the runs' bytes are staged in shared
-// memory in 16-byte granules (rows start at arbitrary byte offsets inside the frame), each
-// thread then converts 4 consecutive pixels per row and stores them as one / three 4-byte words.
-// CTAs are persistent and keep the next two items' bytes in flight with cp.async.
+// The unit of work is a run of 512 pixels of one ROI row, owned by ONE WARP: lane 0 asks the
+// TMA unit for the run's 16-byte granules (one cp.async.bulk per run, rows start at arbitrary
+// byte offsets inside the frame), completion is signalled on a warp-private mbarrier, and each
+// lane converts 16 consecutive pixels and stores them as 16 (V) / 48 (HSV) bytes.  Every warp keeps
+// the next three runs in flight in its own four-stage ring; there is no CTA-wide barrier in the
+// loop.  (ncu history: the first version - one CTA per 4 rows x 1024 px, per-thread 16-byte loads -
+// was issue-bound at 35 instructions per pixel, most of them address arithmetic for the loads.)
 #include "common.cuh"
+#include "tma.cuh"
 #include <algorithm>
 
 namespace rti {
 
-constexpr int ROI_THREADS = 256;
-constexpr int ROI_PIX_PER_THREAD = 4;
-constexpr int ROI_TILE = ROI_THREADS * ROI_PIX_PER_THREAD;       // pixels per work item and row
-constexpr int ROI_STAGE_BYTES = ROI_TILE * 3 + 48;               // + alignment slack both ends, word over-read
-constexpr int ROI_ROWS = 4;                                      // ROI rows per work item
-constexpr int ROI_STAGES = 3;                                    // work items staged ahead per CTA
-constexpr int ROI_CTAS_PER_SM = 5;
-static_assert(ROI_STAGE_BYTES % 16 == 0 && ROI_STAGE_BYTES / 16 <= ROI_THREADS, "one 16-byte granule per thread and row");
-
-// Position of a work item as (column run, row group, frame).  A CTA advances it by its stride,
-// decomposed once by the host, with carries: no division in the item loop.
-struct RoiCursor {
-    int xt, yg, f;
-    __device__ __forceinline__ void advance(int sx, int sy, int sf, int tiles_x, int groups_y) {
-        xt += sx;
-        if (xt >= tiles_x) { xt -= tiles_x; ++yg; }
-        yg += sy;
-        if (yg >= groups_y) { yg -= groups_y; ++f; }
-        f += sf;
-    }
-};
+constexpr int ROI_WARPS = 8;
+constexpr int ROI_THREADS = ROI_WARPS * 32;
+constexpr int ROI_PIX_PER_LANE = 16;                             // 48 B read, 16 / 48 B written per lane and run
+constexpr int ROI_UNIT = 32 * ROI_PIX_PER_LANE;                  // pixels per run
+constexpr int ROI_UNIT_BYTES = ROI_UNIT * 3 + 32;                // + up to 15 B of skew, whole granules, word over-read
+constexpr int ROI_STAGES = 4;                                    // runs per warp: one converted, three in flight
+constexpr int ROI_RING_BYTES = ROI_WARPS * ROI_STAGES * ROI_UNIT_BYTES;    // dynamic shared memory per CTA
+constexpr int ROI_CTAS_PER_SM = 4;                               // resident at most; the host launches 2-4 per SM
+static_assert(ROI_UNIT_BYTES % 16 == 0, "stages hold whole granules");
 
 struct RoiShape {
     int64_t frame_stride, out_stride;
-    int row_pitch, x_min, y_min, rows, cols, tiles_x, groups_y, n_frames;
+    uintptr_t safe_end;                                          // first byte after the last frame
+    int row_pitch, x_min, y_min, rows, cols, segs_x, n_frames;
+    int sx, sy, sf;                                              // the grid's stride in warps as (run, row, frame)
 };
 
-__device__ __forceinline__ void roi_cp_async16(uint32_t smem, const void *gmem, int src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(smem), "l"(gmem), "r"(src_bytes) : "memory");
-}
-
-__device__ __forceinline__ const uint8_t *roi_item_src(const uint8_t *frames, const RoiShape &g, const RoiCursor &c) {
-    return frames + c.f * g.frame_stride + (int64_t)(g.y_min + c.yg * ROI_ROWS) * g.row_pitch +
-           (g.x_min + c.xt * ROI_TILE) * 3;
-}
-
-// ---- request the bytes [a0, a1) of every row of item c in 16-byte granules, one per thread and row.
-// The first granule may start up to 15 bytes before a0 (same frame row or the previous one: inside
-// the allocation), the last one is cut at a1 and zero-filled.  Only the low address bits vary with
-// the row, so the per-row arithmetic is 32-bit.
-__device__ __forceinline__ void roi_issue(uint32_t stage_smem, const uint8_t *__restrict__ frames, const RoiShape &g,
-                                          const RoiCursor &c) {
-    if (c.f < g.n_frames) {
-        const int tid = threadIdx.x;
-        const int nbytes = min(ROI_TILE, g.cols - c.xt * ROI_TILE) * 3;
-        const int nrows = min(ROI_ROWS, g.rows - c.yg * ROI_ROWS);
-        const uint8_t *src0 = roi_item_src(frames, g, c);
-        const uint32_t lo = (uint32_t)(uintptr_t)src0;
-#pragma unroll
-        for (int r = 0; r < ROI_ROWS; ++r) {
-            if (r >= nrows) continue;
-            const int skew = (int)((lo + (uint32_t)(r * g.row_pitch)) & 15u);   // stage[r][skew] = first byte of the run
-            const int left = skew + nbytes - (tid << 4);                        // bytes of the run from this granule on
-            if (left > 0)
-                roi_cp_async16(stage_smem + r * ROI_STAGE_BYTES + (tid << 4),
-                               src0 + ((int64_t)r * g.row_pitch - skew + (tid << 4)), min(16, left));
-        }
+// Position of a run as (run in the row, ROI row, frame).  A warp advances it by the grid's stride,
+// decomposed once by the host, with carries: no division in the loop.
+struct RoiCursor {
+    int xs, y, f;
+    __device__ __forceinline__ void advance(const RoiShape &g) {
+        xs += g.sx;
+        if (xs >= g.segs_x) { xs -= g.segs_x; ++y; }
+        y += g.sy;
+        if (y >= g.rows) { y -= g.rows; ++f; }
+        f += g.sf;
     }
-    asm volatile("cp.async.commit_group;\n" ::: "memory");
+};
+
+__device__ __forceinline__ const uint8_t *roi_run_src(const uint8_t *frames, const RoiShape &g, const RoiCursor &c) {
+    return frames + c.f * g.frame_stride + (int64_t)(g.y_min + c.y) * g.row_pitch + (g.x_min + c.xs * ROI_UNIT) * 3;
 }
 
-// ---- convert 4 pixels per thread and row: the thread's 12 bytes start at skew + 12 tid, i.e.
-// (skew & 3) bytes into a 32-bit word for every thread of the row: 4 word loads + funnel shifts.
-template <bool HSV>
-__device__ __forceinline__ void roi_convert(const uint8_t *stage, const uint8_t *__restrict__ frames,
-                                            uint8_t *__restrict__ out, const RoiShape &g, const RoiCursor &c,
-                                            const int *sdiv, const int *hdiv) {
-    constexpr int BPP = HSV ? 3 : 1;
-    const int tid = threadIdx.x;
-    const int x0 = c.xt * ROI_TILE, y0 = c.yg * ROI_ROWS;
-    const int npix = min(ROI_TILE, g.cols - x0);
-    const int nrows = min(ROI_ROWS, g.rows - y0);
-    const int p0 = tid * ROI_PIX_PER_THREAD;
-    if (p0 >= npix) return;
-    const int cnt = min(ROI_PIX_PER_THREAD, npix - p0);
-    const uint32_t lo = (uint32_t)(uintptr_t)roi_item_src(frames, g, c);
-    uint8_t *dst0 = out + c.f * g.out_stride + ((int64_t)y0 * g.cols + x0 + p0) * BPP;
-#pragma unroll
-    for (int r = 0; r < ROI_ROWS; ++r) {
-        if (r >= nrows) continue;
-        const int o = (int)((lo + (uint32_t)(r * g.row_pitch)) & 15u) + p0 * 3;
-        const uint32_t *wsrc = reinterpret_cast<const uint32_t *>(stage + r * ROI_STAGE_BYTES + (o & ~3));
-        const unsigned sh = (unsigned)(o & 3) * 8u;
-        const uint32_t w0 = wsrc[0], w1 = wsrc[1], w2 = wsrc[2], w3 = wsrc[3];
-        uint32_t in[3];                                          // b0 g0 r0 b1 | g1 r1 b2 g2 | r2 b3 g3 r3
-        in[0] = __funnelshift_r(w0, w1, sh);
-        in[1] = __funnelshift_r(w1, w2, sh);
-        in[2] = __funnelshift_r(w2, w3, sh);
-        uint8_t *dst = dst0 + (int64_t)r * g.cols * BPP;
-        if (!HSV) {
-            // V = max(b, g, r) for two pixels per instruction: each channel's bytes go to the HIGH
-            // byte of a 16-bit lane (the low byte is whatever PRMT leaves there; it only breaks ties),
-            // one three-input u16x2 max, and the four high bytes are packed into the output word.
-            const uint32_t bA = __byte_perm(in[0], in[1], 0x3000), gA = __byte_perm(in[0], in[1], 0x4010),
-                           rA = __byte_perm(in[0], in[1], 0x5020);
-            const uint32_t bB = __byte_perm(in[1], in[2], 0x5020), gB = __byte_perm(in[1], in[2], 0x6030),
-                           rB = __byte_perm(in[1], in[2], 0x7040);
-            const uint32_t vA = __vimax3_u16x2(bA, gA, rA), vB = __vimax3_u16x2(bB, gB, rB);
-            const uint32_t word = __byte_perm(vA, vB, 0x7531);
-            if (cnt == ROI_PIX_PER_THREAD && ((uintptr_t)dst & 3) == 0) {
-                *reinterpret_cast<uint32_t *>(dst) = word;
-            } else {
-                for (int k = 0; k < cnt; ++k) dst[k] = (uint8_t)(word >> (8 * k));
-            }
-            continue;
-        }
-        uint32_t res[3] = {0u, 0u, 0u};
-#pragma unroll
-        for (int k = 0; k < ROI_PIX_PER_THREAD; ++k) {
-            const int b = (in[(3 * k) >> 2] >> (8 * ((3 * k) & 3))) & 0xff;
-            const int gg = (in[(3 * k + 1) >> 2] >> (8 * ((3 * k + 1) & 3))) & 0xff;
-            const int rr = (in[(3 * k + 2) >> 2] >> (8 * ((3 * k + 2) & 3))) & 0xff;
-            const int v = max(max(b, gg), rr);
-            const int diff = v - min(min(b, gg), rr);
-            const int sat = (diff * sdiv[v] + (1 << 11)) >> 12;
-            int h = (v == rr) ? (gg - b) : (v == gg) ? (b - rr + 2 * diff) : (rr - gg + 4 * diff);
-            h = (h * hdiv[diff] + (1 << 11)) >> 12;
-            h += h < 0 ? 180 : 0;
-            res[(3 * k) >> 2] |= (uint32_t)h << (8 * ((3 * k) & 3));
-            res[(3 * k + 1) >> 2] |= (uint32_t)sat << (8 * ((3 * k + 1) & 3));
-            res[(3 * k + 2) >> 2] |= (uint32_t)v << (8 * ((3 * k + 2) & 3));
-        }
-        if (cnt == ROI_PIX_PER_THREAD && ((uintptr_t)dst & 3) == 0) {
-#pragma unroll
-            for (int w = 0; w < 3; ++w) reinterpret_cast<uint32_t *>(dst)[w] = res[w];
-        } else {
-            for (int k = 0; k < cnt * 3; ++k) dst[k] = (uint8_t)(res[k >> 2] >> (8 * (k & 3)));
-        }
+__device__ __forceinline__ void roi_bulk_load(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// Lane 0: request the granules that cover the run.  The first granule may start up to 15 bytes
+// before the run (same frame row or the previous one: inside the buffer); the last one may end up
+// to 15 bytes after it, which is read too unless the frame buffer itself ends there (then the
+// consumer copies the last < 16 bytes itself, see roi_wait).
+__device__ __forceinline__ void roi_request(uint32_t stage, uint32_t bar, const uint8_t *__restrict__ frames,
+                                            const RoiShape &g, const RoiCursor &c) {
+    if (c.f >= g.n_frames) return;
+    const uint8_t *src = roi_run_src(frames, g, c);
+    const uint32_t skew = (uint32_t)(uintptr_t)src & 15u;
+    const uint32_t span = skew + (uint32_t)min(ROI_UNIT, g.cols - c.xs * ROI_UNIT) * 3u;
+    uint32_t bytes = (span + 15u) & ~15u;
+    if ((uintptr_t)(src - skew) + bytes > g.safe_end) bytes = span & ~15u;
+    if (bytes) {
+        mbar_expect_tx(bar, bytes);
+        roi_bulk_load(stage, src - skew, bytes, bar);
+    } else {
+        mbar_arrive(bar);
     }
 }
 
-// Persistent: a CTA walks work items (frame, group of ROI_ROWS rows, run of ROI_TILE columns) with a
-// stride of gridDim.x = (sx, sy, sf); the bytes of the next two items are in flight (cp.async into a
-// three-stage ring) while the current one is converted, so a CTA never waits on a cold load.
+// All lanes: wait for the run's bytes; returns the skew of the run inside its stage.
+__device__ __forceinline__ uint32_t roi_wait(uint8_t *stage, uint32_t bar, uint32_t parity,
+                                             const uint8_t *__restrict__ frames, const RoiShape &g,
+                                             const RoiCursor &c) {
+    const uint8_t *src = roi_run_src(frames, g, c);
+    const uint32_t skew = (uint32_t)(uintptr_t)src & 15u;
+    const uint32_t span = skew + (uint32_t)min(ROI_UNIT, g.cols - c.xs * ROI_UNIT) * 3u;
+    mbar_wait(bar, parity);
+    if ((uintptr_t)(src - skew) + ((span + 15u) & ~15u) > g.safe_end) {      // the buffer's very last granule
+        for (uint32_t k = (span & ~15u) + (threadIdx.x & 31); k < span; k += 32) stage[k] = (src - skew)[k];
+        __syncwarp();
+    }
+    return skew;
+}
+
+// max(b, g, r) of four pixels held in three words b0 g0 r0 b1 | g1 r1 b2 g2 | r2 b3 g3 r3: each
+// channel's bytes go to the HIGH byte of a 16-bit lane (the low byte is whatever PRMT leaves
+// there; it only breaks ties), one three-input u16x2 max per pixel pair, and the four high bytes
+// are packed into one word.
+__device__ __forceinline__ uint32_t roi_max4(uint32_t i0, uint32_t i1, uint32_t i2) {
+    const uint32_t bA = __byte_perm(i0, i1, 0x3000), gA = __byte_perm(i0, i1, 0x4010), rA = __byte_perm(i0, i1, 0x5020);
+    const uint32_t bB = __byte_perm(i1, i2, 0x5020), gB = __byte_perm(i1, i2, 0x6030), rB = __byte_perm(i1, i2, 0x7040);
+    return __byte_perm(__vimax3_u16x2(bA, gA, rA), __vimax3_u16x2(bB, gB, rB), 0x7531);
+}
+
+// OpenCV's 8-bit BGR -> HSV of pixel k (0..3) of three words, written into the same layout.
+__device__ __forceinline__ void roi_hsv1(const uint32_t *in, uint32_t *res, int k, const int *sdiv, const int *hdiv) {
+    const int b = (in[(3 * k) >> 2] >> (8 * ((3 * k) & 3))) & 0xff;
+    const int gg = (in[(3 * k + 1) >> 2] >> (8 * ((3 * k + 1) & 3))) & 0xff;
+    const int rr = (in[(3 * k + 2) >> 2] >> (8 * ((3 * k + 2) & 3))) & 0xff;
+    const int v = max(max(b, gg), rr);
+    const int diff = v - min(min(b, gg), rr);
+    const int sat = (diff * sdiv[v] + (1 << 11)) >> 12;
+    int h = (v == rr) ? (gg - b) : (v == gg) ? (b - rr + 2 * diff) : (rr - gg + 4 * diff);
+    h = (h * hdiv[diff] + (1 << 11)) >> 12;
+    h += h < 0 ? 180 : 0;
+    res[(3 * k) >> 2] |= (uint32_t)h << (8 * ((3 * k) & 3));
+    res[(3 * k + 1) >> 2] |= (uint32_t)sat << (8 * ((3 * k + 1) & 3));
+    res[(3 * k + 2) >> 2] |= (uint32_t)v << (8 * ((3 * k + 2) & 3));
+}
+
 template <bool HSV>
 __global__ void __launch_bounds__(ROI_THREADS, ROI_CTAS_PER_SM)
-roi_extract_kernel(const uint8_t *__restrict__ frames, uint8_t *__restrict__ out, const RoiShape g, int sx, int sy,
-                   int sf) {
-    __shared__ __align__(16) uint8_t ring[ROI_STAGES][ROI_ROWS * ROI_STAGE_BYTES];
+roi_extract_kernel(const uint8_t *__restrict__ frames, uint8_t *__restrict__ out, const RoiShape g) {
+    extern __shared__ __align__(16) uint8_t roi_ring[];          // [ROI_WARPS][ROI_STAGES][ROI_UNIT_BYTES]
+    __shared__ __align__(8) uint64_t bars[ROI_WARPS][ROI_STAGES];
     __shared__ int sdiv[HSV ? 256 : 1];
     __shared__ int hdiv[HSV ? 256 : 1];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (HSV) {
         // tables as OpenCV builds them: saturate_cast<int>(x) = rint(x) for doubles
         const int i = threadIdx.x;
         sdiv[i] = i ? __double2int_rn((double)(255 << 12) / (double)i) : 0;
         hdiv[i] = i ? __double2int_rn((double)(180 << 12) / (6.0 * (double)i)) : 0;
+        __syncthreads();
     }
-    const uint32_t ring_smem = (uint32_t)__cvta_generic_to_shared(&ring[0][0]);
-    constexpr uint32_t STAGE_BYTES = ROI_ROWS * ROI_STAGE_BYTES;
+    const uint32_t ring0 = smem_u32(roi_ring + warp * ROI_STAGES * ROI_UNIT_BYTES), bar0 = smem_u32(&bars[warp][0]);
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < ROI_STAGES; ++s) mbar_init(bar0 + 8 * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
 
-    // item blockIdx.x (< tiles_x * groups_y * n_frames, the host sizes the grid so)
-    RoiCursor cur;                                               // the item being converted
-    cur.xt = (int)(blockIdx.x % g.tiles_x);
-    cur.yg = (int)((blockIdx.x / g.tiles_x) % g.groups_y);
-    cur.f = (int)(blockIdx.x / g.tiles_x / g.groups_y);
-    RoiCursor ahead = cur;                                       // the item being requested
-    roi_issue(ring_smem, frames, g, ahead);
-    ahead.advance(sx, sy, sf, g.tiles_x, g.groups_y);
-    roi_issue(ring_smem + STAGE_BYTES, frames, g, ahead);
-    int stage = 0;
-    for (; cur.f < g.n_frames; cur.advance(sx, sy, sf, g.tiles_x, g.groups_y), stage = stage + 1 == ROI_STAGES ? 0 : stage + 1) {
-        asm volatile("cp.async.wait_group 1;\n" ::: "memory");   // this item has landed (the next may be in flight)
-        __syncthreads();                                         // ... for every thread; the previous item is converted
-        ahead.advance(sx, sy, sf, g.tiles_x, g.groups_y);
-        roi_issue(ring_smem + (stage == 0 ? ROI_STAGES - 1 : stage - 1) * STAGE_BYTES, frames, g, ahead);
-        roi_convert<HSV>(ring[stage], frames, out, g, cur, sdiv, hdiv);
+    // run blockIdx.x * ROI_WARPS + warp, then every (sx, sy, sf)
+    const unsigned gw = blockIdx.x * ROI_WARPS + warp;
+    RoiCursor cur;                                               // the run being converted
+    cur.xs = (int)(gw % g.segs_x);
+    cur.y = (int)((gw / g.segs_x) % g.rows);
+    cur.f = (int)(gw / g.segs_x / g.rows);
+    RoiCursor ahead = cur;                                       // the run being requested
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < ROI_STAGES - 1; ++s) {
+            roi_request(ring0 + s * ROI_UNIT_BYTES, bar0 + 8 * s, frames, g, ahead);
+            ahead.advance(g);
+        }
     }
-    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+    constexpr int BPP = HSV ? 3 : 1;
+    for (unsigned it = 0; cur.f < g.n_frames; ++it, cur.advance(g)) {
+        const unsigned s = it % ROI_STAGES;
+        __syncwarp();                                            // every lane has read the stage of run it - 1
+        if (lane == 0) {
+            const unsigned sn = (it + ROI_STAGES - 1) % ROI_STAGES;
+            roi_request(ring0 + sn * ROI_UNIT_BYTES, bar0 + 8 * sn, frames, g, ahead);
+            ahead.advance(g);
+        }
+        uint8_t *stage = roi_ring + (warp * ROI_STAGES + s) * ROI_UNIT_BYTES;
+        const uint32_t skew = roi_wait(stage, bar0 + 8 * s, (it / ROI_STAGES) & 1u, frames, g, cur);
+
+        // the lane's 48 bytes start at skew + 48 lane, i.e. (skew & 3) bytes into a 32-bit word for
+        // every lane of the run: 13 word loads + funnel shifts
+        constexpr int NW = ROI_PIX_PER_LANE * 3 / 4, NQ = ROI_PIX_PER_LANE / 4;
+        const uint32_t o = skew + lane * (ROI_PIX_PER_LANE * 3);
+        const uint32_t *wsrc = reinterpret_cast<const uint32_t *>(stage + (o & ~3u));
+        const unsigned sh = (o & 3u) * 8u;
+        uint32_t w[NW + 1], in[NW];
+#pragma unroll
+        for (int j = 0; j < NW + 1; ++j) w[j] = wsrc[j];
+#pragma unroll
+        for (int j = 0; j < NW; ++j) in[j] = __funnelshift_r(w[j], w[j + 1], sh);
+
+        const int p0 = cur.xs * ROI_UNIT + lane * ROI_PIX_PER_LANE;
+        const int cnt = min(ROI_PIX_PER_LANE, g.cols - p0);
+        if (cnt <= 0) continue;
+        uint8_t *dst = out + cur.f * g.out_stride + ((int64_t)cur.y * g.cols + p0) * BPP;
+        uint32_t res[NQ * BPP];
+        if constexpr (!HSV) {
+#pragma unroll
+            for (int q = 0; q < NQ; ++q) res[q] = roi_max4(in[3 * q], in[3 * q + 1], in[3 * q + 2]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < NW; ++j) res[j] = 0u;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+#pragma unroll
+                for (int q = 0; q < NQ; ++q) roi_hsv1(in + 3 * q, res + 3 * q, k, sdiv, hdiv);
+        }
+        if (cnt == ROI_PIX_PER_LANE && ((uintptr_t)dst & 15) == 0 && (NQ * BPP) % 4 == 0) {
+#pragma unroll
+            for (int j = 0; j < NQ * BPP / 4; ++j)
+                reinterpret_cast<uint4 *>(dst)[j] = make_uint4(res[4 * j], res[4 * j + 1], res[4 * j + 2], res[4 * j + 3]);
+        } else if (cnt == ROI_PIX_PER_LANE && ((uintptr_t)dst & 7) == 0) {
+#pragma unroll
+            for (int j = 0; j < NQ * BPP / 2; ++j)
+                reinterpret_cast<uint2 *>(dst)[j] = make_uint2(res[2 * j], res[2 * j + 1]);
+        } else if (cnt == ROI_PIX_PER_LANE && ((uintptr_t)dst & 3) == 0) {
+#pragma unroll
+            for (int j = 0; j < NQ * BPP; ++j) reinterpret_cast<uint32_t *>(dst)[j] = res[j];
+        } else {
+#pragma unroll
+            for (int j = 0; j < NQ * BPP; ++j)
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (4 * j + q < cnt * BPP) dst[4 * j + q] = (uint8_t)(res[j] >> (8 * q));
+        }
+    }
 }
 
 }  // namespace rti
@@ -206,22 +238,35 @@ extern "C" int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n
     const int64_t bpp = hsv ? 3 : 1;
     RTI_REQUIRE(frame_stride >= (int64_t)height * width * 3 || n_frames == 1, "rti_roi_extract: frame stride too small");
     RTI_REQUIRE(out_stride >= (int64_t)rows * cols * bpp || n_frames == 1, "rti_roi_extract: output stride too small");
-    const int tiles_x = (cols + ROI_TILE - 1) / ROI_TILE, groups_y = (rows + ROI_ROWS - 1) / ROI_ROWS;
-    const int64_t n_items = (int64_t)tiles_x * groups_y * n_frames;
+    RTI_REQUIRE((int64_t)width * 3 < (int64_t)1 << 30, "rti_roi_extract: frame rows too wide");
+    RoiShape g;
+    g.frame_stride = frame_stride; g.out_stride = out_stride; g.row_pitch = width * 3;
+    g.safe_end = (uintptr_t)d_bgr + (uintptr_t)((int64_t)(n_frames - 1) * frame_stride + (int64_t)height * width * 3);
+    g.x_min = x_min; g.y_min = y_min; g.rows = rows; g.cols = cols; g.n_frames = n_frames;
+    g.segs_x = (cols + ROI_UNIT - 1) / ROI_UNIT;
+    const int64_t n_units = (int64_t)g.segs_x * rows * n_frames;
     int dev = 0, sms = 148;
     RTI_CUDA(cudaGetDevice(&dev));
     RTI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    const int grid = (int)std::min<int64_t>(n_items, (int64_t)sms * ROI_CTAS_PER_SM);
-    const int sx = grid % tiles_x, sy = (grid / tiles_x) % groups_y, sf = grid / tiles_x / groups_y;   // the stride as (run, group, frame)
-    RTI_REQUIRE((int64_t)width * 3 * ROI_ROWS < (int64_t)1 << 31, "rti_roi_extract: frame rows too wide");
-    RoiShape g;
-    g.frame_stride = frame_stride; g.out_stride = out_stride; g.row_pitch = width * 3;
-    g.x_min = x_min; g.y_min = y_min; g.rows = rows; g.cols = cols;
-    g.tiles_x = tiles_x; g.groups_y = groups_y; g.n_frames = n_frames;
+    // CTAs per SM, measured (tools/prof_roi.py; 40 x 2048^2 out of 3840 x 2160 | 300 x 400^2 out of 1920 x 1080):
+    //   V    1: 0.166 | 0.064 ms   2: 0.113 | 0.045   3: 0.123 | 0.041   4: 0.186 | 0.044   5 (3 stages): 0.213 | 0.049
+    //   HSV  1: 0.436 | 0.172 ms   2: 0.316 | 0.120   3: 0.284 | 0.109   4: 0.277 | 0.105
+    // HSV is bound by its integer arithmetic and wants every warp it can get; the V stream is fastest with
+    // 16-24 warps per SM (more TMA requests in flight than that slow it down).
+    const int per_sm = hsv ? ROI_CTAS_PER_SM : (cols >= 4 * ROI_UNIT ? 2 : 3);
+    const int grid = (int)std::min<int64_t>((n_units + ROI_WARPS - 1) / ROI_WARPS, (int64_t)sms * per_sm);
+    const int stride = grid * ROI_WARPS;                         // in runs, as (run, row, frame)
+    g.sx = stride % g.segs_x; g.sy = (stride / g.segs_x) % rows; g.sf = stride / g.segs_x / rows;
+    static bool configured = false;                              // idempotent: racing first calls set the same value
+    if (!configured) {
+        RTI_CUDA(cudaFuncSetAttribute(roi_extract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ROI_RING_BYTES));
+        RTI_CUDA(cudaFuncSetAttribute(roi_extract_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ROI_RING_BYTES));
+        configured = true;
+    }
     if (hsv)
-        roi_extract_kernel<true><<<grid, ROI_THREADS, 0, as_stream(stream)>>>(d_bgr, d_out, g, sx, sy, sf);
+        roi_extract_kernel<true><<<grid, ROI_THREADS, ROI_RING_BYTES, as_stream(stream)>>>(d_bgr, d_out, g);
     else
-        roi_extract_kernel<false><<<grid, ROI_THREADS, 0, as_stream(stream)>>>(d_bgr, d_out, g, sx, sy, sf);
+        roi_extract_kernel<false><<<grid, ROI_THREADS, ROI_RING_BYTES, as_stream(stream)>>>(d_bgr, d_out, g);
     RTI_LAUNCHED("roi_extract_kernel");
     return RTI_OK;
 }

@@ -155,11 +155,14 @@ def test_gpu_roi_stays_inside_its_buffers(torch_cuda):
     h, w = 21, 37
     frame = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
     d = torch.from_numpy(frame).cuda()
-    for hsv, bpp in ((0, 1), (1, 3)):
+    held = torch.zeros(h * w * 3 + 64, dtype=torch.uint8, device="cuda")     # the same frame at an odd address
+    held[13:13 + h * w * 3] = d.reshape(-1)
+    for hsv, bpp, src in ((0, 1, d.data_ptr()), (1, 3, d.data_ptr()), (0, 1, held.data_ptr() + 13),
+                          (1, 3, held.data_ptr() + 13)):
         rows, cols, x0, y0 = 9, 30, 7, 12                     # ends at the frame's last pixel
         guard = 256
         out = torch.full((guard + rows * cols * bpp + guard,), 0xAB, dtype=torch.uint8, device="cuda")
-        _capi.call("rti_roi_extract", d.data_ptr(), h * w * 3, 1, h, w, x0, y0, rows, cols, hsv,
+        _capi.call("rti_roi_extract", src, h * w * 3, 1, h, w, x0, y0, rows, cols, hsv,
                    out.data_ptr() + guard, rows * cols * bpp, None)
         torch.cuda.synchronize()
         o = out.cpu().numpy()
