@@ -89,16 +89,22 @@ ptm_grids_kernel(const double *__restrict__ coef, int64_t plane_stride, int64_t 
     extern __shared__ double s_axis[];
     for (int i = threadIdx.x; i < g; i += GRIDS_THREADS) s_axis[i] = axis[i];
     __syncthreads();
-    const int64_t gg = (int64_t)g * g;
+    // direction d = v g + u walked by the thread in steps of the CTA size, as (v, u) with a carry:
+    // a 64-bit d / g per table entry was 46 instructions per entry and made the kernel issue-bound
+    const int gg = g * g;
+    const int u0 = threadIdx.x % g, v0 = threadIdx.x / g, du = GRIDS_THREADS % g, dv = GRIDS_THREADS / g;
     for (int64_t p = blockIdx.x; p < n_pixels; p += gridDim.x) {
         double a[6];
 #pragma unroll
         for (int k = 0; k < 6; ++k) a[k] = __ldg(coef + k * plane_stride + p);
         double *dst = grids + p * gg;
-        for (int64_t d = threadIdx.x; d < gg; d += GRIDS_THREADS) {
-            const int v = (int)(d / g), u = (int)(d - (int64_t)v * g);
+        int u = u0, v = v0;
+        for (int d = threadIdx.x; d < gg; d += GRIDS_THREADS) {
             const double lv = s_axis[v], lu = s_axis[u];
             __stcs(dst + d, ptm_eval(a[0], ptm_bv(a, lv), ptm_cv(a, lv), lu));
+            u += du;
+            v += dv;
+            if (u >= g) { u -= g; ++v; }
         }
     }
 }
