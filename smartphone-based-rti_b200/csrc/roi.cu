@@ -257,12 +257,11 @@ extern "C" int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n
     const int grid = (int)std::min<int64_t>((n_units + ROI_WARPS - 1) / ROI_WARPS, (int64_t)sms * per_sm);
     const int stride = grid * ROI_WARPS;                         // in runs, as (run, row, frame)
     g.sx = stride % g.segs_x; g.sy = (stride / g.segs_x) % rows; g.sf = stride / g.segs_x / rows;
-    static bool configured = false;                              // idempotent: racing first calls set the same value
-    if (!configured) {
+    // per launch (microseconds): the attribute belongs to the current device's copy of the kernel
+    if (hsv)
         RTI_CUDA(cudaFuncSetAttribute(roi_extract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ROI_RING_BYTES));
+    else
         RTI_CUDA(cudaFuncSetAttribute(roi_extract_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ROI_RING_BYTES));
-        configured = true;
-    }
     if (hsv)
         roi_extract_kernel<true><<<grid, ROI_THREADS, ROI_RING_BYTES, as_stream(stream)>>>(d_bgr, d_out, g);
     else
