@@ -109,6 +109,10 @@ __device__ __forceinline__ uint32_t roi_max4(uint32_t i0, uint32_t i1, uint32_t 
 }
 
 // OpenCV's 8-bit BGR -> HSV of pixel k (0..3) of three words, written into the same layout.
+// (Measured and not adopted: the hue as selects of its operands instead of the nested ternary, which
+// compiles to two divergent branches per pixel: 0.277 -> 0.282 ms; the lanes' 48-byte outputs exchanged
+// through the consumed stage and stored as coalesced 512-byte instructions: 0.307 ms.  The HSV
+// path is bound by its ~40 integer instructions per pixel, not by branches or the store pattern.)
 __device__ __forceinline__ void roi_hsv1(const uint32_t *in, uint32_t *res, int k, const int *sdiv, const int *hdiv) {
     const int b = (in[(3 * k) >> 2] >> (8 * ((3 * k) & 3))) & 0xff;
     const int gg = (in[(3 * k + 1) >> 2] >> (8 * ((3 * k + 1) & 3))) & 0xff;
