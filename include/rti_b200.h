@@ -245,7 +245,10 @@ int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, const uint8
  * per frame (the relighter's HSV ROI, interactive_relighting.py:109); hsv == 0:
  * only V = max(B,G,R), uint8 [rows][cols] per frame = one frame of the stack that
  * compute_intensities reads (FeatureMatcher.py:183-184).  out_stride in bytes.
- * The ROI bounds (centre, clamping quirks) are host arithmetic, see roi.py. */
+ * The ROI bounds (centre, clamping quirks) are host arithmetic, see roi.py.
+ * Any byte alignment of d_bgr, the frame rows and d_out is accepted.  Rows are read in whole
+ * 16-byte granules: up to 15 bytes before a run (never before the 16-byte granule that holds
+ * d_bgr[0]) and after it (never past the last frame's end) are touched but not used. */
 int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n_frames, int height,
                     int width, int x_min, int y_min, int rows, int cols, int hsv,
                     uint8_t *d_out, int64_t out_stride, rti_stream_t stream);
