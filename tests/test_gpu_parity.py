@@ -292,6 +292,25 @@ def test_ptm_grids_vs_oracle(torch_cuda):
     assert np.max(np.abs(grids.cpu().numpy() - ref)) <= 1e-12 * np.max(np.abs(ref))
 
 
+@pytest.mark.parametrize("g", [1, 7, 255, 256, 257, 300])
+def test_ptm_grids_any_axis_length(torch_cuda, g):
+    """The kernel walks directions d = v g + u in steps of its CTA size with a (v, u) carry: axis lengths
+    below, at and above the CTA size, checked against the oracle's grid evaluation."""
+    from rti_b200 import _capi
+    torch = torch_cuda
+    p = 5
+    coef = _random_coef(p, seed=g)
+    ax = np.linspace(-1.0, 1.0, g) if g > 1 else np.array([0.25])
+    grids = torch.full((p, g, g), np.nan, dtype=torch.float64, device="cuda")
+    _capi.call("rti_ptm_grids", dev(torch, coef).data_ptr(), p, p, dev(torch, ax).data_ptr(), g,
+               grids.data_ptr(), None)
+    torch.cuda.synchronize()
+    ref = orc.ptm_grid(coef.T, ax)
+    got = grids.cpu().numpy()
+    assert got.shape == ref.shape and np.all(np.isfinite(got))
+    assert np.max(np.abs(got - ref)) <= 1e-12 * max(np.max(np.abs(ref)), 1.0)
+
+
 def test_grids_to_table_transposes_and_truncates(torch_cuda):
     from rti_b200 import _capi
     torch = torch_cuda
