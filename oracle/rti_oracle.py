@@ -51,21 +51,25 @@ def light_axis(step: float = 0.02) -> np.ndarray:
 
 
 # ------------------------------------------------------------------------- gather
-def gather_soa(frames, cams, rows: int | None = None, cols: int | None = None):
+def gather_soa(frames, cams, rows: int | None = None, cols: int | None = None, row0: int = 0,
+               col0: int = 0):
     """Light vectors and intensities per pixel and frame (analysis.py:217-232).
 
     frames: (N, H, W) uint8, cams: (N, 3) float64 (camera position per frame).
     For pixel p=(x, y, 0) and frame i: l = (cam_i - p) / ||cam_i - p|| in fp64;
     l[0], l[1] are stored as float32, the intensity as int32, all with the frame
     index fastest: arrays of shape (rows, cols, N).
+
+    row0 / col0: `frames` is the window of the ROI that starts at pixel (x, y) = (col0, row0);
+    the reference walks the whole ROI, a window evaluates the same formula for its pixels.
     """
     frames = np.asarray(frames)
     cams = np.asarray(cams, dtype=np.float64)
     n = frames.shape[0]
     rows = frames.shape[1] if rows is None else rows
     cols = frames.shape[2] if cols is None else cols
-    ys = np.arange(rows, dtype=np.float64)[:, None, None]
-    xs = np.arange(cols, dtype=np.float64)[None, :, None]
+    ys = np.arange(row0, row0 + rows, dtype=np.float64)[:, None, None]
+    xs = np.arange(col0, col0 + cols, dtype=np.float64)[None, :, None]
     dx = cams[None, None, :, 0] - xs                      # (1, cols, N)
     dy = cams[None, None, :, 1] - ys                      # (rows, 1, N)
     dz = cams[None, None, :, 2]

@@ -105,7 +105,9 @@ def check_table(table, vals, tol_abs):
 
 
 @pytest.mark.parametrize("n,p,step", [(40, 36, 0.25), (64, 256, 0.1), (96, 1000, 0.1), (130, 700, 0.02),
-                                      (300, 520, 0.05), (7, 5, 0.5)])
+                                      (300, 520, 0.05), (7, 5, 0.5),
+                                      # the bench's and config 4's light counts, >= 8 pixel blocks of 256
+                                      (500, 2048, 0.1), (1000, 2304, 0.1)])
 def test_shared_grid_values_and_table_vs_oracle(torch_cuda, n, p, step):
     lx, ly = shared_nodes(n, seed=n)
     axis = orc.light_axis(step)
@@ -118,11 +120,15 @@ def test_shared_grid_values_and_table_vs_oracle(torch_cuda, n, p, step):
     scale = np.max(np.abs(vals))
     got = sh.apply_f64(packed, p).T                       # (G*G, P)
     err = np.max(np.abs(got - vals)) / scale
-    assert err <= GRID_RTOL_ACHIEVED, err
+    # cond(A) grows with the node count (~1e6 at n = 1000): the fp64 operator carries cond * 1e-16
+    # and the fp16 hi+lo split 2^-22 of each row maximum, against values that cancel down to 0..255
+    achieved = GRID_RTOL_ACHIEVED if n < 500 else 2e-4
+    print("shared-light n=%d: grid error %.2e of the largest value" % (n, err))
+    assert err <= achieved, err
     assert err <= GRID_RTOL
     table = sh.table(packed, p)
     assert int(sh.bad.item()) == 0
-    flips = check_table(table, vals, GRID_RTOL_ACHIEVED * scale)
+    flips = check_table(table, vals, achieved * scale)
     assert flips <= 1e-3 * table.size + 2
     # the float path and the table path are the same accumulators: trunc(float) == table exactly
     assert np.array_equal(np.trunc(got).astype(np.int32), table)
