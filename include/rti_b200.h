@@ -222,19 +222,23 @@ int rti_rbf_shared_apply_f64(const uint16_t *d_packed, int n, int64_t n_pixels, 
  * interactive_relighting.py:35-36).  d_hsv: uint8 [n_pixels][3] HSV ROI or NULL.
  * With d_hsv the value replaces V and the pixel is converted with OpenCV's 8-bit
  * COLOR_HSV2BGR arithmetic into d_out uint8 [n_pixels][3]; with d_hsv == NULL
- * d_out is uint8 [n_pixels] (the V plane only). */
-int rti_relight_ptm(const double *d_coef, int64_t plane_stride, int64_t n_pixels,
+ * d_out is uint8 [n_pixels] (the V plane only).
+ * row_width: columns of the ROI image (n_pixels = rows * row_width).  cv2.cvtColor converts
+ * row by row and its scalar tail -- the last row_width % 32 pixels of every row on an AVX2
+ * host -- rounds x*255 half to even where the vector body truncates; the kernels reproduce
+ * that per pixel column.  row_width == 0: vector-body arithmetic for every pixel. */
+int rti_relight_ptm(const double *d_coef, int64_t plane_stride, int64_t n_pixels, int row_width,
                     double lu, double lv, const uint8_t *d_hsv, uint8_t *d_out,
                     rti_stream_t stream);
 /* same from a float32 coefficient map (24 B/pixel; the fp32 evaluation can differ
  * from the table by 1 where the fp64 value is within ~1e-4 of an integer) */
-int rti_relight_ptm_f32(const float *d_coef, int64_t plane_stride, int64_t n_pixels,
+int rti_relight_ptm_f32(const float *d_coef, int64_t plane_stride, int64_t n_pixels, int row_width,
                         float lu, float lv, const uint8_t *d_hsv, uint8_t *d_out,
                         rti_stream_t stream);
 /* float64 -> float32 planar coefficient copy for rti_relight_ptm_f32 */
 int rti_coef_to_f32(const double *d_coef, int64_t n_values, float *d_out, rti_stream_t stream);
 /* table lookup variant: clamp an int32 table image to [0,255] and convert */
-int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, const uint8_t *d_hsv,
+int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, int row_width, const uint8_t *d_hsv,
                            uint8_t *d_out, rti_stream_t stream);
 
 /* ---- ROI extraction upstream of the path ---------------------------

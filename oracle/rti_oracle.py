@@ -262,19 +262,23 @@ def clamp_values(img) -> np.ndarray:
     return np.clip(np.asarray(img), 0, 255)
 
 
-def hsv2bgr_u8(hsv) -> np.ndarray:
+def hsv2bgr_u8(hsv, simd_lanes: int = 32) -> np.ndarray:
     """8-bit HSV -> BGR with OpenCV's cv2.COLOR_HSV2BGR semantics
     (interactive_relighting.py:38): H in [0,180), S and V in [0,255].
 
     OpenCV is third-party to the reference (no version pinned; 4.13.0 in the
-    build container).  This restates what its vectorised 8-bit kernel computes,
-    established by exhaustive comparison over all 180*256*256 inputs
-    (tests/golden/make_golden.py, 0 mismatches): h' = H*(6/180), sector =
+    build container).  This restates what its 8-bit kernel computes, established
+    by exhaustive comparison over all 180*256*256 inputs, once with every pixel in
+    the vector body and once with every pixel in the scalar tail
+    (tests/golden/make_golden.py, 0 mismatches each): h' = H*(6/180), sector =
     trunc(h'), f = h' - sector, s = S/255, v = V/255 in float32,
         p = v*(1 - s), q = v*fma(-s, f, 1), t = v*fma(-s, 1 - f, 1),
-    channel = TRUNCATE(x * 255).  (OpenCV's scalar tail, used for the last
-    < 64 pixels of a buffer, rounds instead of truncating; callers comparing
-    against cv2 on arbitrary images must allow 1 LSB there.)
+    channel = TRUNCATE(x * 255) in the vector body, ROUND-half-even(x * 255) in
+    the scalar tail.  cvtColor converts image rows one at a time, so for a
+    (rows, cols, 3) image the tail is the last cols % simd_lanes pixels OF EACH ROW
+    (columns >= cols - cols % simd_lanes); simd_lanes = 32 is the uint8 lane count
+    of the AVX2 build that runs here and on the GPU box's host (16 on an SSE-only
+    host).  Inputs without a row structure (ndim != 3) are treated as vector body.
     """
     hsv = np.asarray(hsv, dtype=np.uint8)
     f32 = np.float32
@@ -295,7 +299,13 @@ def hsv2bgr_u8(hsv) -> np.ndarray:
     tab = np.stack([v, t1, t2, t3], axis=-1)
     sel = np.array([[1, 3, 0], [1, 0, 2], [3, 0, 1], [0, 2, 1], [0, 1, 3], [2, 1, 0]])
     bgr = np.take_along_axis(tab, sel[sector], axis=-1)   # b, g, r table slots
-    return np.clip(np.trunc(bgr * f32(255.0)), 0, 255).astype(np.uint8)
+    scaled = bgr * f32(255.0)
+    out = np.trunc(scaled)
+    if hsv.ndim == 3 and simd_lanes > 0:
+        cols = hsv.shape[1]
+        tail = cols - cols % simd_lanes
+        out[:, tail:] = np.rint(scaled[:, tail:])          # cvRound: round half to even
+    return np.clip(out, 0, 255).astype(np.uint8)
 
 
 def relight_from_table(table, hsv_roi, lx: float, ly: float) -> np.ndarray:

@@ -70,10 +70,10 @@ SIGNATURES = {
     "rti_rbf_shared_pack_soa": (_i, [_p, _l, _i, _p, _p, _p]),
     "rti_rbf_shared_table": (_i, [_p, _i, _l, _p, _p, _p, _i, _p, _l, _p, _p]),
     "rti_rbf_shared_apply_f64": (_i, [_p, _i, _l, _p, _p, _p, _i, _p, _p]),
-    "rti_relight_ptm": (_i, [_p, _l, _l, _d, _d, _p, _p, _p]),
-    "rti_relight_ptm_f32": (_i, [_p, _l, _l, _f, _f, _p, _p, _p]),
+    "rti_relight_ptm": (_i, [_p, _l, _l, _i, _d, _d, _p, _p, _p]),
+    "rti_relight_ptm_f32": (_i, [_p, _l, _l, _i, _f, _f, _p, _p, _p]),
     "rti_coef_to_f32": (_i, [_p, _l, _p, _p]),
-    "rti_relight_from_image": (_i, [_p, _l, _p, _p, _p]),
+    "rti_relight_from_image": (_i, [_p, _l, _i, _p, _p, _p]),
     "rti_roi_extract": (_i, [_p, _l, _i, _i, _i, _i, _i, _i, _i, _i, _p, _l, _p]),
     "rti_ptm_compute_host": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p, _i]),
     "rti_destroy": (_i, []),

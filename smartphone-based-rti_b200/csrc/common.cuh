@@ -186,8 +186,15 @@ __device__ __forceinline__ double ptm_eval(double a0, double bv, double cv, doub
 // float64 -> int32 like numpy's element assignment: truncate toward zero.
 __device__ __forceinline__ int trunc_i32(double v) { return __double2int_rz(v); }
 
-// OpenCV 8-bit COLOR_HSV2BGR (see oracle/rti_oracle.py hsv2bgr_u8 for the derivation).
-__device__ __forceinline__ void hsv2bgr_u8(int h8, int s8, int v8, uint8_t &b, uint8_t &g, uint8_t &r) {
+// OpenCV 8-bit COLOR_HSV2BGR (see oracle/rti_oracle.py hsv2bgr_u8 for the derivation).  cvtColor
+// works row by row: the vector body truncates x*255, the scalar tail of each row (the last
+// cols % 32 pixels on an AVX2 host) rounds half to even; `tail` selects the latter.
+__device__ __forceinline__ bool hsv_row_tail(int64_t p, int row_width) {
+    if (row_width <= 0) return false;
+    const int x = (int)(p % row_width);
+    return x >= row_width - (row_width & 31);
+}
+__device__ __forceinline__ void hsv2bgr_u8(int h8, int s8, int v8, bool tail, uint8_t &b, uint8_t &g, uint8_t &r) {
     const float h = __fmul_rn((float)h8, (float)(6.0 / 180.0));
     const float s = __fmul_rn((float)s8, (float)(1.0 / 255.0));
     const float v = __fmul_rn((float)v8, (float)(1.0 / 255.0));
@@ -207,8 +214,9 @@ __device__ __forceinline__ void hsv2bgr_u8(int h8, int s8, int v8, uint8_t &b, u
         case 4: fb = t0; fg = t1; fr = t3; break;
         default: fb = t2; fg = t1; fr = t0; break;
     }
-    const int ib = (int)__fmul_rn(fb, 255.0f), ig = (int)__fmul_rn(fg, 255.0f),
-              ir = (int)__fmul_rn(fr, 255.0f);
+    const float xb = __fmul_rn(fb, 255.0f), xg = __fmul_rn(fg, 255.0f), xr = __fmul_rn(fr, 255.0f);
+    const int ib = tail ? __float2int_rn(xb) : (int)xb, ig = tail ? __float2int_rn(xg) : (int)xg,
+              ir = tail ? __float2int_rn(xr) : (int)xr;
     b = (uint8_t)min(max(ib, 0), 255);
     g = (uint8_t)min(max(ig, 0), 255);
     r = (uint8_t)min(max(ir, 0), 255);

@@ -119,7 +119,7 @@ __device__ __forceinline__ int clamp_u8(int v) { return min(max(v, 0), 255); }  
 
 template <typename T, bool HSV>
 __global__ void __launch_bounds__(RELIGHT_THREADS)
-relight_kernel(const T *__restrict__ coef, int64_t plane_stride, int64_t n_pixels, T lu, T lv,
+relight_kernel(const T *__restrict__ coef, int64_t plane_stride, int64_t n_pixels, int row_width, T lu, T lv,
                const uint8_t *__restrict__ hsv, uint8_t *__restrict__ out) {
     const int64_t p0 = ((int64_t)blockIdx.x * RELIGHT_THREADS + threadIdx.x) * 4;
     if (p0 >= n_pixels) return;
@@ -171,7 +171,7 @@ relight_kernel(const T *__restrict__ coef, int64_t plane_stride, int64_t n_pixel
         for (int q = 0; q < 4 && p0 + q < n_pixels; ++q) {
             const uint8_t *px = hsv + (p0 + q) * 3;
             uint8_t b, g, r;
-            hsv2bgr_u8(px[0], px[1], val[q], b, g, r);
+            hsv2bgr_u8(px[0], px[1], val[q], hsv_row_tail(p0 + q, row_width), b, g, r);
             uint8_t *o = out + (p0 + q) * 3;
             o[0] = b; o[1] = g; o[2] = r;
         }
@@ -180,7 +180,7 @@ relight_kernel(const T *__restrict__ coef, int64_t plane_stride, int64_t n_pixel
 
 template <bool HSV>
 __global__ void __launch_bounds__(RELIGHT_THREADS)
-relight_image_kernel(const int32_t *__restrict__ image, int64_t n_pixels,
+relight_image_kernel(const int32_t *__restrict__ image, int64_t n_pixels, int row_width,
                      const uint8_t *__restrict__ hsv, uint8_t *__restrict__ out) {
     const int64_t p = (int64_t)blockIdx.x * RELIGHT_THREADS + threadIdx.x;
     if (p >= n_pixels) return;
@@ -189,7 +189,7 @@ relight_image_kernel(const int32_t *__restrict__ image, int64_t n_pixels,
         out[p] = (uint8_t)v;
     } else {
         uint8_t b, g, r;
-        hsv2bgr_u8(hsv[p * 3], hsv[p * 3 + 1], v, b, g, r);
+        hsv2bgr_u8(hsv[p * 3], hsv[p * 3 + 1], v, hsv_row_tail(p, row_width), b, g, r);
         out[p * 3] = b; out[p * 3 + 1] = g; out[p * 3 + 2] = r;
     }
 }
@@ -281,32 +281,32 @@ extern "C" int rti_ptm_grids(const double *d_coef, int64_t plane_stride, int64_t
     return RTI_OK;
 }
 
-extern "C" int rti_relight_ptm(const double *d_coef, int64_t plane_stride, int64_t n_pixels, double lu,
-                               double lv, const uint8_t *d_hsv, uint8_t *d_out, rti_stream_t stream) {
+extern "C" int rti_relight_ptm(const double *d_coef, int64_t plane_stride, int64_t n_pixels, int row_width,
+                               double lu, double lv, const uint8_t *d_hsv, uint8_t *d_out, rti_stream_t stream) {
     RTI_REQUIRE(d_coef && d_out, "rti_relight_ptm: NULL pointer");
-    RTI_REQUIRE(n_pixels > 0 && plane_stride >= n_pixels, "rti_relight_ptm: bad sizes");
+    RTI_REQUIRE(n_pixels > 0 && plane_stride >= n_pixels && row_width >= 0, "rti_relight_ptm: bad sizes");
     const int64_t blocks = (n_pixels + RELIGHT_THREADS * 4 - 1) / (RELIGHT_THREADS * 4);
     if (d_hsv)
         relight_kernel<double, true><<<(unsigned)blocks, RELIGHT_THREADS, 0, as_stream(stream)>>>(
-            d_coef, plane_stride, n_pixels, lu, lv, d_hsv, d_out);
+            d_coef, plane_stride, n_pixels, row_width, lu, lv, d_hsv, d_out);
     else
         relight_kernel<double, false><<<(unsigned)blocks, RELIGHT_THREADS, 0, as_stream(stream)>>>(
-            d_coef, plane_stride, n_pixels, lu, lv, nullptr, d_out);
+            d_coef, plane_stride, n_pixels, row_width, lu, lv, nullptr, d_out);
     RTI_LAUNCHED("relight_kernel<double>");
     return RTI_OK;
 }
 
-extern "C" int rti_relight_ptm_f32(const float *d_coef, int64_t plane_stride, int64_t n_pixels, float lu,
-                                   float lv, const uint8_t *d_hsv, uint8_t *d_out, rti_stream_t stream) {
+extern "C" int rti_relight_ptm_f32(const float *d_coef, int64_t plane_stride, int64_t n_pixels, int row_width,
+                                   float lu, float lv, const uint8_t *d_hsv, uint8_t *d_out, rti_stream_t stream) {
     RTI_REQUIRE(d_coef && d_out, "rti_relight_ptm_f32: NULL pointer");
-    RTI_REQUIRE(n_pixels > 0 && plane_stride >= n_pixels, "rti_relight_ptm_f32: bad sizes");
+    RTI_REQUIRE(n_pixels > 0 && plane_stride >= n_pixels && row_width >= 0, "rti_relight_ptm_f32: bad sizes");
     const int64_t blocks = (n_pixels + RELIGHT_THREADS * 4 - 1) / (RELIGHT_THREADS * 4);
     if (d_hsv)
         relight_kernel<float, true><<<(unsigned)blocks, RELIGHT_THREADS, 0, as_stream(stream)>>>(
-            d_coef, plane_stride, n_pixels, lu, lv, d_hsv, d_out);
+            d_coef, plane_stride, n_pixels, row_width, lu, lv, d_hsv, d_out);
     else
         relight_kernel<float, false><<<(unsigned)blocks, RELIGHT_THREADS, 0, as_stream(stream)>>>(
-            d_coef, plane_stride, n_pixels, lu, lv, nullptr, d_out);
+            d_coef, plane_stride, n_pixels, row_width, lu, lv, nullptr, d_out);
     RTI_LAUNCHED("relight_kernel<float>");
     return RTI_OK;
 }
@@ -318,16 +318,16 @@ extern "C" int rti_coef_to_f32(const double *d_coef, int64_t n_values, float *d_
     return RTI_OK;
 }
 
-extern "C" int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, const uint8_t *d_hsv,
-                                      uint8_t *d_out, rti_stream_t stream) {
-    RTI_REQUIRE(d_image && d_out && n_pixels > 0, "rti_relight_from_image: bad arguments");
+extern "C" int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, int row_width,
+                                      const uint8_t *d_hsv, uint8_t *d_out, rti_stream_t stream) {
+    RTI_REQUIRE(d_image && d_out && n_pixels > 0 && row_width >= 0, "rti_relight_from_image: bad arguments");
     const int64_t blocks = (n_pixels + RELIGHT_THREADS - 1) / RELIGHT_THREADS;
     if (d_hsv)
         relight_image_kernel<true><<<(unsigned)blocks, RELIGHT_THREADS, 0, as_stream(stream)>>>(
-            d_image, n_pixels, d_hsv, d_out);
+            d_image, n_pixels, row_width, d_hsv, d_out);
     else
         relight_image_kernel<false><<<(unsigned)blocks, RELIGHT_THREADS, 0, as_stream(stream)>>>(
-            d_image, n_pixels, nullptr, d_out);
+            d_image, n_pixels, row_width, nullptr, d_out);
     RTI_LAUNCHED("relight_image_kernel");
     return RTI_OK;
 }

@@ -30,7 +30,8 @@ class Relighter:
 
     coef: float64 (6, P) device tensor or ndarray (an InterpolationResult also works);
     hsv_roi: optional uint8 (rows, cols, 3) HSV image whose V channel is replaced and which is
-    converted HSV->BGR like cv2.cvtColor (interactive_relighting.py:37-38).
+    converted HSV->BGR like cv2.cvtColor (interactive_relighting.py:37-38), including its per-row
+    scalar tail (the last cols % 32 pixels of a row round where the vector body truncates).
     precision 'f64' reproduces the table values bit for bit at grid nodes; 'f32' halves the
     bytes read per frame.
     """
@@ -65,7 +66,7 @@ class Relighter:
         torch = _torch()
         hsv_ptr = self.hsv.data_ptr() if self.hsv is not None else None
         name = "rti_relight_ptm" if self.precision == "f64" else "rti_relight_ptm_f32"
-        _capi.call(name, self.coef.data_ptr(), self.p, self.p, float(lu), float(lv), hsv_ptr,
+        _capi.call(name, self.coef.data_ptr(), self.p, self.p, self.cols, float(lu), float(lv), hsv_ptr,
                    self.out.data_ptr(), _stream_ptr(torch))
         return self.out
 
@@ -89,6 +90,6 @@ def relight_from_table(image, hsv_roi=None):
     if hsv_roi is not None:
         hsv = torch.from_numpy(np.ascontiguousarray(hsv_roi, dtype=np.uint8)).cuda()
     out = torch.empty((rows, cols, 3) if hsv is not None else (rows, cols), dtype=torch.uint8, device="cuda")
-    _capi.call("rti_relight_from_image", img.data_ptr(), rows * cols,
+    _capi.call("rti_relight_from_image", img.data_ptr(), rows * cols, cols,
                hsv.data_ptr() if hsv is not None else None, out.data_ptr(), _stream_ptr(torch))
     return out.cpu().numpy()

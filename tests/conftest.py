@@ -39,3 +39,8 @@ def ref_rbf_n96():
 @pytest.fixture(scope="session")
 def relight_golden():
     return dict(np.load(os.path.join(GOLDEN, "relight.npz")))
+
+
+@pytest.fixture(scope="session")
+def relight_rows_golden():
+    return dict(np.load(os.path.join(GOLDEN, "relight_rows.npz")))

@@ -15,6 +15,10 @@ Writes
                     and a random HSV image with cv2.cvtColor(HSV2BGR) output
     roi.npz         ut.get_ROI(img, corners, hsv=True) crops of a seeded BGR image
                     (`make_golden.py roi` regenerates only this one)
+    relight_rows.npz cv2.cvtColor(HSV2BGR) of images whose width is not a multiple of the
+                    SIMD width (the reference's default 400-wide ROI among them): cvtColor's
+                    per-row scalar tail rounds where its vector body truncates
+                    (`make_golden.py relight_rows` regenerates only this one)
 and checks the oracle's HSV->BGR and BGR->HSV restatements exhaustively against cv2.
 """
 import os
@@ -100,12 +104,42 @@ def make_roi_golden(cst, ut, orc):
     print("BGR2HSV exhaustive mismatches vs cv2 %s: %d of %d" % (cv2.__version__, bad, cube.size))
 
 
+def make_relight_rows_golden(orc):
+    """relight_rows.npz: what interactive_relighting.py:38 returns for ROI widths with a scalar
+    tail (400 = the reference's ROI_DIAMETER, 399, 37, 31) and without one (64)."""
+    import cv2
+    rng = np.random.default_rng(11)
+    out = {"cv2_version": np.array(cv2.__version__)}
+    for rows, cols in ((12, 400), (5, 399), (9, 37), (7, 31), (3, 64)):
+        hsv = np.stack([rng.integers(0, 180, (rows, cols)), rng.integers(0, 256, (rows, cols)),
+                        rng.integers(0, 256, (rows, cols))], -1).astype(np.uint8)
+        bgr = cv2.cvtColor(hsv, cv2.COLOR_HSV2BGR)
+        out["hsv_%dx%d" % (rows, cols)] = hsv
+        out["bgr_%dx%d" % (rows, cols)] = bgr
+        print("relight_rows %dx%d: oracle mismatches %d, vector-body-only mismatches %d"
+              % (rows, cols, np.count_nonzero(orc.hsv2bgr_u8(hsv) != bgr),
+                 np.count_nonzero(orc.hsv2bgr_u8(hsv, simd_lanes=0) != bgr)))
+    np.savez_compressed(os.path.join(HERE, "relight_rows.npz"), **out)
+    # exhaustive: every (H, S, V) once in the vector body (width 256) and once in the tail (width 31)
+    hh, ss, vv = np.meshgrid(np.arange(180, dtype=np.uint8), np.arange(256, dtype=np.uint8),
+                             np.arange(256, dtype=np.uint8), indexing="ij")
+    flat = np.stack([hh, ss, vv], -1).reshape(-1, 3)
+    body = flat.reshape(180 * 256, 256, 3)
+    pad = (-flat.shape[0]) % 31
+    tail = np.concatenate([flat, np.zeros((pad, 3), np.uint8)]).reshape(-1, 31, 3)
+    for name, img in (("vector body", body), ("scalar tail", tail)):
+        bad = np.count_nonzero(cv2.cvtColor(img, cv2.COLOR_HSV2BGR) != orc.hsv2bgr_u8(img))
+        print("HSV2BGR exhaustive (%s) mismatches vs cv2 %s: %d of %d" % (name, cv2.__version__, bad, img.size))
+
+
 def main():
     analysis, cst, ut = import_reference()
     sys.path.insert(0, os.path.join(HERE, "..", "..", "oracle"))
     import rti_oracle as orc
     if sys.argv[1:] == ["roi"]:
         return make_roi_golden(cst, ut, orc)
+    if sys.argv[1:] == ["relight_rows"]:
+        return make_relight_rows_golden(orc)
 
     # ---- small end-to-end case --------------------------------------------------
     R, N = 6, 40
@@ -180,6 +214,7 @@ def main():
           max(np.max(np.abs(og[y, x] - rbf[y][x])) / np.max(np.abs(rbf[y][x])) for y, x in keep))
     print("rbf table mismatches", np.count_nonzero(orc.table_from_grids(og) != tab_rbf))
     make_roi_golden(cst, ut, orc)
+    make_relight_rows_golden(orc)
 
 
 if __name__ == "__main__":

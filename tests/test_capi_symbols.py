@@ -56,7 +56,7 @@ def test_argument_errors_without_gpu(lib):
     assert lib.rti_ptm_fit_frames(p, 3, p, 8, 0, 2, 2, p, 4, None, None) == _capi.RTI_ERR_ARG
     assert lib.rti_ptm_table(p, 2, 4, p, 100, p, 4, None, None) == _capi.RTI_ERR_ARG
     assert lib.rti_ptm_table(p, 4, 4, p, 0, p, 4, None, None) == _capi.RTI_ERR_ARG
-    assert lib.rti_relight_ptm(p, 4, 0, 0.0, 0.0, None, p, None) == _capi.RTI_ERR_ARG
+    assert lib.rti_relight_ptm(p, 4, 0, 0, 0.0, 0.0, None, p, None) == _capi.RTI_ERR_ARG
     assert lib.rti_ptm_compute_host(p, p, 8, 4, 4, 2, 4, p, 100, p, None, 0) == _capi.RTI_ERR_ARG
     with pytest.raises(_capi.RtiError):
         _capi.check(_capi.RTI_ERR_ARG)

@@ -358,6 +358,25 @@ def test_relight_reproduces_table_at_grid_nodes(torch_cuda, relight_golden):
             tab[orc.light_to_index(ly)][orc.light_to_index(lx)], hsv), ref_bgr)
 
 
+def test_hsv2bgr_device_row_tail_matches_cv2_golden(torch_cuda, relight_rows_golden):
+    """Widths with a scalar tail (400 is the reference's ROI_DIAMETER): table-lookup and PTM relight
+    kernels against cv2.cvtColor's own output (interactive_relighting.py:37-38)."""
+    from rti_b200 import relighting
+    torch = torch_cuda
+    g = relight_rows_golden
+    for key in [k for k in g if k.startswith("hsv_")]:
+        hsv, bgr = g[key], g["bgr_" + key[4:]]
+        rows, cols = hsv.shape[:2]
+        out = relighting.relight_from_table(hsv[:, :, 2].astype(np.int32), hsv)
+        assert np.array_equal(out, bgr), key
+        # constant-polynomial coefficient map whose value is the V channel: same image through relight_kernel
+        coef = np.zeros((6, rows * cols))
+        coef[5] = hsv[:, :, 2].reshape(-1) + 0.25
+        for prec in ("f64", "f32"):
+            img = relighting.Relighter(dev(torch, coef), rows, cols, hsv_roi=hsv, precision=prec).render(0.3, -0.6)
+            assert np.array_equal(img.cpu().numpy(), bgr), (key, prec)
+
+
 def test_relight_f32_map_within_one(torch_cuda):
     from rti_b200 import relighting
     torch = torch_cuda

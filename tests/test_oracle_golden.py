@@ -125,5 +125,19 @@ def test_hsv2bgr_matches_cv2_golden(relight_golden):
     assert np.array_equal(orc.hsv2bgr_u8(relight_golden["hsv"]), relight_golden["bgr"])
 
 
+def test_hsv2bgr_row_tail_matches_cv2_golden(relight_rows_golden):
+    """cvtColor's scalar tail (the last cols % 32 pixels of each row) rounds, the body truncates:
+    the reference's default 400-wide ROI has a 16-pixel tail per row."""
+    g = relight_rows_golden
+    shapes = [k[4:] for k in g if k.startswith("hsv_")]
+    assert "12x400" in shapes and len(shapes) >= 5
+    tail_hits = 0
+    for sh in shapes:
+        hsv, bgr = g["hsv_" + sh], g["bgr_" + sh]
+        assert np.array_equal(orc.hsv2bgr_u8(hsv), bgr), sh
+        tail_hits += np.count_nonzero(orc.hsv2bgr_u8(hsv, simd_lanes=0) != bgr)
+    assert tail_hits > 0                      # the goldens do exercise the rounding tail
+
+
 def test_clamp():
     assert np.array_equal(orc.clamp_values(np.array([-5, 0, 1, 255, 256, 4000])), [0, 0, 1, 255, 255, 255])

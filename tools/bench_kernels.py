@@ -162,7 +162,7 @@ def main():
             def one():
                 lu, lv = dirs[state["i"] % 1000]
                 state["i"] += 1
-                _capi.call(fn_name, cmap.data_ptr(), P, P, lu, lv, hsv_t.data_ptr() if hsv_t is not None else None,
+                _capi.call(fn_name, cmap.data_ptr(), P, P, R, lu, lv, hsv_t.data_ptr() if hsv_t is not None else None,
                            o.data_ptr(), S)
             # the coefficient map (403 / 201 MB) exceeds L2, no flush needed
             ms, best = tm.run(one, reps=50, flush=False)
