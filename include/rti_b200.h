@@ -264,7 +264,9 @@ int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n_frames, in
  * float64 [6][rows*cols] come back (either may be NULL).  Row tiles are streamed:
  * H2D of tile t+1, fit + table of tile t and D2H of tile t-1 overlap on three
  * streams.  Uses the current device; `tile_rows` <= 0 picks a default.  Blocks
- * until the result is in host memory. */
+ * until the result is in host memory.  The cached workspace (streams, tile buffers) is
+ * per device ordinal: calls for different devices run concurrently (one host thread per
+ * GPU), calls for the same device serialise on that device's workspace. */
 int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cams, int n,
                          int rows_total, int cols, int row0, int rows,
                          const double *h_axis, int g,

@@ -60,7 +60,8 @@ def _stack_frames(data, rows, cols):
         if roi.ndim != 2 or roi.shape[0] < rows or roi.shape[1] < cols:
             # the reference raises IndexError at intensities[y][x] (analysis.py:232)
             raise IndexError("frame %d ROI has shape %s, need at least (%d, %d)" % (i, roi.shape, rows, cols))
-        frames[i] = roi[:rows, :cols]
+        from .ingest import roi_as_uint8
+        frames[i] = roi_as_uint8(roi[:rows, :cols], i)
         cams[i] = np.asarray(rec[1], dtype=np.float64).reshape(3)
     return frames, cams
 
@@ -624,6 +625,8 @@ def write_on_file(data, filename, compressed=True):
     else:
         filename = filename + ".pickle"
         slab = table_io.is_table_slab(data)          # the nested list of views prepare_images_data returns
+        if slab is not None and not table_io.template_ok(slab.shape[2:], slab.dtype):
+            slab = None                              # this numpy pickles ndarrays differently: plain pickle.dump
         with open(filename, "wb") as f:
             if slab is not None and slab.nbytes > 0:
                 table_io.dump_table(slab, f)         # same object graph, no per-image copies

@@ -125,7 +125,12 @@ struct NormalEq {
 };
 
 // Solve the 6x6 normal equations by Cholesky (fp64, fully unrolled, in registers).
-// Returns false when a pivot is not positive (rank-deficient pixel).
+// Returns false when a pivot is not positive (rank-deficient pixel) or has lost more than 12
+// digits against its diagonal entry: pivot_j / G_jj <= 1e-12 means cond(G) >~ 1e12, i.e. a design
+// matrix with cond >~ 1e6 (light directions nearly on a line / a conic), where the normal
+// equations can no longer deliver north_star's 1e-4 against the reference's SVD
+// (analysis.py:295-298).  Such pixels are reported as singular instead of returned silently off.
+constexpr double PTM_PIVOT_RTOL = 1e-12;
 __device__ __forceinline__ bool solve_normal_eq(const NormalEq &ne, double count, double a[6]) {
     double L[6][6];
     int k = 0;
@@ -139,10 +144,11 @@ __device__ __forceinline__ bool solve_normal_eq(const NormalEq &ne, double count
     bool ok = true;
 #pragma unroll
     for (int j = 0; j < 6; ++j) {
-        double d = L[j][j];
+        const double d0 = L[j][j];
+        double d = d0;
 #pragma unroll
         for (int p = 0; p < j; ++p) d = fma(-L[j][p], L[j][p], d);
-        ok = ok && (d > 0.0);
+        ok = ok && (d > PTM_PIVOT_RTOL * d0);
         const double inv = rsqrt(d);
         L[j][j] = d * inv;                                   // sqrt(d)
 #pragma unroll
@@ -168,6 +174,10 @@ __device__ __forceinline__ bool solve_normal_eq(const NormalEq &ne, double count
 #pragma unroll
         for (int p = i + 1; p < 6; ++p) v = fma(-L[p][i], a[p], v);
         a[i] = v / L[i][i];
+    }
+    if (!ok) {                                               // flagged pixels carry NaN, never a plausible-looking value
+#pragma unroll
+        for (int i = 0; i < 6; ++i) a[i] = __longlong_as_double(0x7FF8000000000000LL);
     }
     return ok;
 }

@@ -20,8 +20,11 @@ struct HostPipe {
     bool ready = false;
 };
 
-static HostPipe g_pipe;
-static std::mutex g_pipe_mutex;
+// One workspace per device ordinal, each behind its own mutex: calls for different devices (one
+// host thread per GPU) run concurrently, calls for the same device serialise on its workspace.
+constexpr int MAX_DEVICES = 64;
+static HostPipe g_pipes[MAX_DEVICES];
+static std::mutex g_pipe_mutex[MAX_DEVICES];
 
 static int grow(void **ptr, size_t *have, size_t need) {
     if (*have >= need && *ptr) return RTI_OK;
@@ -47,12 +50,8 @@ static int pipe_release(HostPipe &c) {
     return RTI_OK;
 }
 
-static int pipe_init(HostPipe &c) {
-    int dev = 0;
-    RTI_CUDA(cudaGetDevice(&dev));
-    if (c.ready && c.device == dev) return RTI_OK;
-    pipe_release(c);
-    RTI_CUDA(cudaSetDevice(dev));
+static int pipe_init(HostPipe &c, int dev) {
+    if (c.ready) return RTI_OK;
     c.device = dev;
     RTI_CUDA(cudaStreamCreateWithFlags(&c.s_h2d, cudaStreamNonBlocking));
     RTI_CUDA(cudaStreamCreateWithFlags(&c.s_comp, cudaStreamNonBlocking));
@@ -84,9 +83,12 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
         set_error("rti_ptm_compute_host: PTM needs >= 6 light samples, got %d", n);
         return n <= 0 ? RTI_ERR_ARG : RTI_ERR_TOO_FEW;
     }
-    std::lock_guard<std::mutex> lock(g_pipe_mutex);
-    HostPipe &c = g_pipe;
-    int rc = pipe_init(c);
+    int dev = 0;
+    RTI_CUDA(cudaGetDevice(&dev));
+    RTI_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "rti_ptm_compute_host: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_pipe_mutex[dev]);
+    HostPipe &c = g_pipes[dev];
+    int rc = pipe_init(c, dev);
     if (rc != RTI_OK) return rc;
 
     const int64_t gg = (int64_t)g * g;
@@ -174,6 +176,12 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
 
 extern "C" int rti_destroy(void) {
     release_tile_counters();
-    std::lock_guard<std::mutex> lock(g_pipe_mutex);
-    return pipe_release(g_pipe);
+    int cur = 0;
+    const bool have_cur = cudaGetDevice(&cur) == cudaSuccess;
+    for (int d = 0; d < MAX_DEVICES; ++d) {
+        std::lock_guard<std::mutex> lock(g_pipe_mutex[d]);
+        pipe_release(g_pipes[d]);
+    }
+    if (have_cur) cudaSetDevice(cur);
+    return RTI_OK;
 }

@@ -194,6 +194,26 @@ def read_pbz2(path, threads=None):
         reader.close()
 
 
+def roi_as_uint8(roi, index):
+    """The ROI intensities of one frame record as uint8 without silent wrap-around.  The reference
+    stores intensities[y][x] into an int32 array (analysis.py:219, 232) and so keeps any integer; the
+    CUDA path carries uint8 frames (what FeatureMatcher.py:183-184 emits), so anything else must be
+    integral and inside [0, 255] -- otherwise it is an error, not a modulo-256 value."""
+    roi = np.asarray(roi)
+    if roi.dtype == np.uint8:
+        return roi
+    if roi.dtype == np.bool_ or not np.issubdtype(roi.dtype, np.number) or np.iscomplexobj(roi):
+        raise ValueError("frame %d: ROI intensities have dtype %s; uint8 expected" % (index, roi.dtype))
+    if roi.size:
+        lo, hi = roi.min(), roi.max()
+        if not (lo >= 0 and hi <= 255):
+            raise ValueError("frame %d: ROI intensities span [%s, %s], outside the uint8 range of the "
+                             "frame records (FeatureMatcher.py:183-184)" % (index, lo, hi))
+        if not np.issubdtype(roi.dtype, np.integer) and not np.all(roi == np.rint(roi)):
+            raise ValueError("frame %d: non-integral ROI intensities (dtype %s)" % (index, roi.dtype))
+    return roi.astype(np.uint8)
+
+
 def pinned_stack(records, rows, cols):
     """list[(uint8 (H,W), float64 (3,))] -> pinned uint8 (N, rows, cols) tensor + float64 (N, 3)
     ndarray (the layout of analysis._stack_frames, written once, straight into pinned memory)."""
@@ -206,7 +226,7 @@ def pinned_stack(records, rows, cols):
         roi = np.asarray(rec[0])
         if roi.ndim != 2 or roi.shape[0] < rows or roi.shape[1] < cols:
             raise IndexError("frame %d ROI has shape %s, need at least (%d, %d)" % (i, roi.shape, rows, cols))
-        view[i] = roi[:rows, :cols]
+        view[i] = roi_as_uint8(roi[:rows, :cols], i)
         cams[i] = np.asarray(rec[1], dtype=np.float64).reshape(3)
     return frames, cams
 

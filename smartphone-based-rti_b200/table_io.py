@@ -95,6 +95,17 @@ def is_table_slab(images):
         return None
 
 
+def template_ok(image_shape, dtype) -> bool:
+    """True when the installed numpy pickles an ndarray of this shape the way the streaming writer
+    assumes; callers check BEFORE opening (truncating) the output file and fall back to
+    ``pickle.dump`` otherwise."""
+    try:
+        _array_template(tuple(image_shape), np.dtype(dtype))
+        return True
+    except RuntimeError:
+        return False
+
+
 class TableStreamWriter:
     """Push-style writer of the protocol-4 pickle of ``[[img(v, u) for u in range(gu)] for v in
     range(gv)]``: ``write_images(block)`` takes the next images in row-major order as a C-contiguous

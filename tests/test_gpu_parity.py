@@ -475,6 +475,51 @@ def test_host_pipeline_tiles_match_single_shot(torch_cuda):
     _capi.call("rti_destroy")
 
 
+def _fit_soa(torch, lx, ly, inten):
+    from rti_b200 import _capi
+    p, n = lx.shape
+    coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_soa", dev(torch, lx).data_ptr(), dev(torch, ly).data_ptr(), dev(torch, inten).data_ptr(),
+               p, n, coef.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    return coef.cpu().numpy().T, int(bad.item())
+
+
+def test_ptm_fit_narrow_light_cone_and_near_collinear_lights(torch_cuda):
+    """the kernels solve the normal equations where the reference takes an SVD of the design
+    matrix (analysis.py:294-298).  (a) a narrow light cone (|l| < 0.1: badly SCALED columns) keeps
+    north_star's 1e-4 with a wide margin -- Cholesky is insensitive to column scaling; (b) lights on a
+    line plus jitter (genuinely ill-conditioned, cond(design) >~ 1e6) are reported as singular instead
+    of coming back with half their digits; (c) in between, coefficients hold 1e-4."""
+    torch = torch_cuda
+    rng = np.random.default_rng(12)
+    p, n = 64, 120
+    inten = rng.integers(0, 256, (p, n)).astype(np.int32)
+    # (a) narrow cone
+    lx = rng.uniform(-0.1, 0.1, (p, n)).astype(np.float32)
+    ly = rng.uniform(-0.1, 0.1, (p, n)).astype(np.float32)
+    got, bad = _fit_soa(torch, lx, ly, inten)
+    assert bad == 0
+    ref = orc.ptm_fit_batch(lx, ly, inten)
+    assert coef_rel_err(got, ref) < 1e-7
+    # (b) lights on a line, jitter 1e-7: cond(design) ~ 1e7 or worse
+    t = rng.uniform(-0.9, 0.9, (p, n))
+    lx = t.astype(np.float32)
+    ly = (0.5 * t + 1e-7 * rng.standard_normal((p, n))).astype(np.float32)
+    conds = np.array([np.linalg.cond(orc.ptm_design(lx[i], ly[i])) for i in range(p)])
+    assert conds.min() > 3e6
+    got, bad = _fit_soa(torch, lx, ly, inten)
+    assert bad == p and np.all(np.isnan(got))
+    # (c) jitter 1e-3: cond ~ 1e3-1e5, solvable within the budget
+    ly = (0.5 * t + 1e-3 * rng.standard_normal((p, n))).astype(np.float32)
+    conds = np.array([np.linalg.cond(orc.ptm_design(lx[i], ly[i])) for i in range(p)])
+    assert conds.max() < 1e6
+    got, bad = _fit_soa(torch, lx, ly, inten)
+    assert bad == 0
+    assert coef_rel_err(got, orc.ptm_fit_batch(lx, ly, inten)) < 1e-4
+
+
 # ------------------------------------------------------- properties at BASELINE sizes
 def test_full_size_properties(torch_cuda):
     """Config 3 geometry on a 1024-column slab with N=500: size-independent properties.

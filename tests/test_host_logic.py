@@ -205,3 +205,38 @@ def test_load_table_maps_the_result_pickle(tmp_path):
     raw = open(path + ".pickle", "rb").read()
     open(path + ".pickle", "wb").write(raw[:-7])
     assert table_io.load_table(path + ".pickle") is None
+
+
+def test_frame_records_must_fit_uint8():
+    """an int32 ROI value of 300 must not become 44 silently (the reference keeps it in its
+    int32 array, analysis.py:219/232); in-range integral data of any dtype is accepted as is."""
+    from rti_b200 import ingest
+    roi = np.arange(12, dtype=np.int32).reshape(3, 4) * 20
+    assert np.array_equal(ingest.roi_as_uint8(roi, 0), roi.astype(np.uint8))
+    assert np.array_equal(ingest.roi_as_uint8(roi.astype(np.float64), 0), roi.astype(np.uint8))
+    for bad in (roi + 100, roi - 1, roi.astype(np.float32) + 0.5):
+        with pytest.raises(ValueError):
+            ingest.roi_as_uint8(bad, 3)
+    recs = [(roi + 100, np.zeros(3))]
+    with pytest.raises(ValueError):
+        analysis._stack_frames(recs, 3, 4)
+
+
+def test_write_on_file_falls_back_when_the_template_does_not_apply(tmp_path, monkeypatch):
+    """A numpy whose ndarray pickle opcodes differ must give the reference's plain pickle.dump, decided
+    before the output file is opened."""
+    import pickle
+    from rti_b200 import table_io
+    table = np.arange(2 * 3 * 4 * 5, dtype=np.int32).reshape(2, 3, 4, 5)
+    nested = [[table[v, u] for u in range(3)] for v in range(2)]
+    assert table_io.template_ok((4, 5), np.int32)
+
+    def broken(shape, dtype):
+        raise RuntimeError("unexpected memo opcode")
+    monkeypatch.setattr(table_io, "_array_template", broken)
+    assert not table_io.template_ok((4, 5), np.int32)
+    name = str(tmp_path / "fallback")
+    rti_b200.write_on_file(nested, name, compressed=False)
+    with open(name + ".pickle", "rb") as f:
+        back = pickle.load(f)
+    assert np.array_equal(np.array(back), table)
