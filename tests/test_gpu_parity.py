@@ -511,10 +511,10 @@ def test_ptm_fit_narrow_light_cone_and_near_collinear_lights(torch_cuda):
     assert conds.min() > 3e6
     got, bad = _fit_soa(torch, lx, ly, inten)
     assert bad == p and np.all(np.isnan(got))
-    # (c) jitter 1e-3: cond ~ 1e3-1e5, solvable within the budget
-    ly = (0.5 * t + 1e-3 * rng.standard_normal((p, n))).astype(np.float32)
+    # (c) jitter 1e-2: cond(design) ~ 1e4, solvable within the budget
+    ly = (0.5 * t + 1e-2 * rng.standard_normal((p, n))).astype(np.float32)
     conds = np.array([np.linalg.cond(orc.ptm_design(lx[i], ly[i])) for i in range(p)])
-    assert conds.max() < 1e6
+    assert conds.max() < 1e5
     got, bad = _fit_soa(torch, lx, ly, inten)
     assert bad == 0
     assert coef_rel_err(got, orc.ptm_fit_batch(lx, ly, inten)) < 1e-4
