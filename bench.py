@@ -99,64 +99,116 @@ class ClockSampler(threading.Thread):
 
 
 # ---------------------------------------------------------------------- CPU reference arm
+REF_DIR = os.path.join(ROOT, "baseline", "_ref")
+
+
+def make_config(world):
+    """The `config` object of BOTH arms' JSON lines (key-identical so the driver can compare them)."""
+    return {"workload": WORKLOAD, "rows_per_gpu": ROWS, "cols": COLS, "lights": N_LIGHTS, "grid": [G, G],
+            "parallelism": "row-tile x%d, no collective" % world,
+            "l2": "inputs (524 MB) and the 42 GB table written per step exceed the 126 MB L2"}
+
+
+def _reference_module():
+    """The UNMODIFIED reference analysis.py when a copy sits in baseline/_ref (git-ignored, never
+    committed); matplotlib is stubbed because analysis.py:14 imports it for debug plots only."""
+    if not os.path.isfile(os.path.join(REF_DIR, "analysis.py")):
+        return None
+    import types
+    mpl, plt = types.ModuleType("matplotlib"), types.ModuleType("matplotlib.pyplot")
+    mpl.pyplot = plt
+    sys.modules.setdefault("matplotlib", mpl)
+    sys.modules.setdefault("matplotlib.pyplot", plt)
+    sys.path.insert(0, REF_DIR)
+    cwd = os.getcwd()
+    os.chdir(REF_DIR)
+    try:
+        import analysis
+    except Exception:
+        return None
+    finally:
+        os.chdir(cwd)
+    return analysis
+
+
 def _cpu_worker(args):
-    """Oracle port of the per-pixel path for `count` pixels: full-SVD PTM fit
-    (analysis.py:295-298), grid evaluation (:301-315) and int32 truncation (:404-407)."""
-    seed, count, n = args
+    """The per-pixel path for `count` pixels on one core.  mode "ptm": full-SVD PTM fit
+    (analysis.py:295-298), grid evaluation (:301-315), int32 truncation (:404-407); mode "rbf":
+    scipy Rbf('linear') fit + grid evaluation (analysis.py:249-260) + truncation.  Runs the
+    unmodified reference functions when baseline/_ref holds them, else the oracle port."""
+    seed, count, n, mode = args
     os.environ["OMP_NUM_THREADS"] = "1"
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import rti_oracle as orc
+    ref = _reference_module()
     rng = np.random.default_rng(seed)
     lx = rng.uniform(-0.9, 0.9, (count, n)).astype(np.float32)
     ly = rng.uniform(-0.9, 0.9, (count, n)).astype(np.float32)
     inten = rng.integers(0, 256, (count, n)).astype(np.int32)
     ax = orc.light_axis()
+    xi, yi = np.meshgrid(ax, ax, indexing="ij")
     t0 = time.perf_counter()
     acc = 0
     for p in range(count):
-        grid = orc.ptm_grid(orc.ptm_fit(lx[p], ly[p], inten[p]), ax)
+        if ref is not None:
+            if mode == "ptm":
+                grid = ref._interpolate_PTM(lx[p], ly[p], ax, inten[p])
+            else:
+                grid = ref._interpolate_RBF(lx[p], ly[p], xi, yi, inten[p])
+            grid = np.asarray(grid)
+        elif mode == "ptm":
+            grid = orc.ptm_grid(orc.ptm_fit(lx[p], ly[p], inten[p]), ax)
+        else:
+            grid = orc.rbf_grid(lx[p], ly[p], orc.rbf_fit(lx[p], ly[p], inten[p]), ax)
         acc += int(orc.table_from_grids(grid[None, None])[0, 0, 0, 0])
-    return time.perf_counter() - t0, acc
+    return time.perf_counter() - t0, acc, ref is not None
 
 
-def cpu_reference(pixels_per_core, steps=1, warmup=0):
-    """Times the oracle port on all host cores; returns (Mpixel.lights/s, cores, sample text, ms/step)."""
+def cpu_reference(pixels_per_core, steps=1, warmup=0, mode="ptm", cores=None):
+    """Times the CPU path on `cores` host cores (default: all); returns a cpu_baseline dict + ms/step."""
     import multiprocessing as mp
     try:
         import threadpoolctl
         threadpoolctl.threadpool_limits(1)
     except Exception:
         pass
-    cores = len(os.sched_getaffinity(0))
+    cores = len(os.sched_getaffinity(0)) if cores is None else cores
     ctx = mp.get_context("fork")
     with ctx.Pool(cores) as pool:
-        pool.map(_cpu_worker, [(i, 1, N_LIGHTS) for i in range(cores)])          # warm the workers
+        kind = pool.map(_cpu_worker, [(i, 1, N_LIGHTS, mode) for i in range(cores)])[0][2]    # warm the workers
         for _ in range(warmup):
-            pool.map(_cpu_worker, [(i, pixels_per_core, N_LIGHTS) for i in range(cores)])
+            pool.map(_cpu_worker, [(i, pixels_per_core, N_LIGHTS, mode) for i in range(cores)])
         t0 = time.perf_counter()
         for s in range(max(steps, 1)):
-            pool.map(_cpu_worker, [(1000 * s + i, pixels_per_core, N_LIGHTS) for i in range(cores)])
+            pool.map(_cpu_worker, [(1000 * s + i, pixels_per_core, N_LIGHTS, mode) for i in range(cores)])
         dt = (time.perf_counter() - t0) / max(steps, 1)
     pixels = pixels_per_core * cores
     value = pixels * N_LIGHTS / dt / 1e6
-    sample = ("%d random pixels x %d lights per step (%d per core), oracle port of full-SVD PTM fit + "
-              "100x100 grid eval + int32 truncation; extrapolates linearly in pixels"
-              % (pixels, N_LIGHTS, pixels_per_core))
-    return value, cores, sample, dt * 1e3
+    what = {"ptm": "full-SVD PTM fit + 100x100 grid eval + int32 truncation",
+            "rbf": "linear-RBF solve(A, d) + cdist grid eval + int32 truncation"}[mode]
+    who = "the unmodified reference functions (baseline/_ref)" if kind else "oracle port of"
+    sample = ("%d random pixels x %d lights per step (%d per core), %s %s; extrapolates linearly in pixels"
+              % (pixels, N_LIGHTS, pixels_per_core, who, what))
+    return {"value": value, "unit": UNIT, "cores": cores, "kind": "reference" if kind else "port",
+            "sample": sample}, dt * 1e3
 
 
 def run_reference(args, rank):
     if rank != 0:
         return
-    value, cores, sample, ms = cpu_reference(args.cpu_pixels_per_core, steps=args.steps, warmup=min(args.warmup, 1))
+    cpu, ms = cpu_reference(args.cpu_pixels_per_core, steps=args.steps, warmup=min(args.warmup, 1))
+    one, _ = cpu_reference(max(args.cpu_pixels_per_core // 4, 1), cores=1)
+    cpu["one_core_value"] = one["value"]
+    rbf, _ = cpu_reference(max(args.cpu_pixels_per_core // 12, 1), mode="rbf")
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "impl": "reference", "metric": METRIC, "value": cpu["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "rows": ROWS, "cols": COLS, "lights": N_LIGHTS, "grid": [G, G]},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
-        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "config": make_config(args.gpus),
+        "cpu_baseline": cpu,
+        "e2e": {"value": cpu["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "secondary": {"rbf_per_pixel_lights": {"cpu_baseline": rbf}},
     }
     print(json.dumps(line), flush=True)
 
@@ -249,16 +301,135 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
     return res
 
 
+# ------------------------------------------------------------------ parity sample (checker)
+def parity_sample(frames_of, cams, row0, cols, n_pixels, coef_cols, table_cols, idx):
+    """Holds sampled pixels of a finished run to the CPU oracle (the checker, after the timed region):
+    coefficient columns (6, k) and int32 table columns (G*G, k) of the pixels `idx` (indices into the
+    slab) against orc.gather_soa -> ptm_fit -> ptm_grid -> table_from_grids on the same frames.
+    frames_of(y, x) returns the (N,) uint8 intensities of slab pixel (y, x)."""
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import rti_oracle as orc
+    ax = orc.light_axis()
+    max_rel, mismatch, near = 0.0, 0, 0
+    for j, pix in enumerate(idx):
+        y, x = divmod(int(pix), cols)
+        fr = np.asarray(frames_of(y, x), dtype=np.uint8).reshape(-1, 1, 1)
+        lx, ly, inten = orc.gather_soa(fr, cams, row0=row0 + y, col0=x)
+        ref = orc.ptm_fit(lx[0, 0], ly[0, 0], inten[0, 0])
+        if coef_cols is not None:
+            max_rel = max(max_rel, float(np.abs(coef_cols[:, j] - ref).max() / np.abs(ref).max()))
+        if table_cols is not None:
+            grid = orc.ptm_grid(ref, ax)
+            tab = orc.table_from_grids(grid[None, None])[:, :, 0, 0].reshape(-1)
+            diff = tab != table_cols[:, j]
+            # an entry may differ only where the fp64 value sits within 1e-9 of an integer (SURVEY 7.3e)
+            frac = np.abs(grid.reshape(-1) - np.rint(grid.reshape(-1)))
+            near += int(np.count_nonzero(diff & (frac < 1e-9)))
+            mismatch += int(np.count_nonzero(diff & ~(frac < 1e-9)))
+    return {"pixels": int(len(idx)), "max_rel": max_rel, "table_mismatch": mismatch,
+            "table_integer_boundary_flips": near, "oracle": "oracle/rti_oracle.py (fp64 SVD fit)"}
+
+
+# ------------------------------------------- BASELINE configs[3], strong-scaled, with the gather
+def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
+    """synthetic 4096x4096 ROI x 1000 lights, PTM: the ROI rows are split over the ranks
+    (sharding.row_partition); every rank streams its slab through the fused kernel in sub-slabs of
+    256 rows into ONE reused 42 GB table buffer (the 671 GB table cannot be resident anywhere), then
+    the fp64 coefficient map (805 MB in total) is gathered to rank 0 over NCCL (sharding.gather_planar).
+    Device-timed, max over ranks; strong scaling (total work fixed)."""
+    from rti_b200 import sharding, synthetic
+    import rti_b200
+    R4, N4, SUB = 4096, 1000, 256
+    r0, nr = sharding.row_partition(R4, world)[rank]
+    P_loc = nr * R4
+    S = torch.cuda.current_stream().cuda_stream
+    gen = torch.Generator(device="cuda").manual_seed(100 + rank)
+    frames = torch.empty((N4, nr, R4), dtype=torch.uint8, device="cuda")
+    for i in range(0, N4, 50):
+        frames[i:i + 50] = torch.randint(0, 256, (min(50, N4 - i), nr, R4), dtype=torch.uint8, device="cuda",
+                                         generator=gen)
+    cams = synthetic.camera_positions(R4, R4, N4, np.random.default_rng(0))
+    d_cams = torch.from_numpy(cams).cuda()
+    d_axis = torch.from_numpy(rti_b200.light_axis(0.02)).cuda()
+    coef = torch.empty((6, P_loc), dtype=torch.float64, device="cuda")
+    sub_px = SUB * R4
+    table = torch.empty((G * G, sub_px), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(2, dtype=torch.int32, device="cuda")
+
+    def run_ptm():
+        for y in range(0, nr, SUB):
+            rr = min(SUB, nr - y)
+            _capi.call("rti_ptm_fit_table_frames", frames.data_ptr() + y * R4, P_loc, d_cams.data_ptr(), N4,
+                       r0 + y, rr, R4, d_axis.data_ptr(), G, coef.data_ptr() + 8 * y * R4, P_loc,
+                       table.data_ptr(), sub_px, bad.data_ptr(), S)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    run_ptm()                                                        # warm-up
+    full = sharding.gather_planar(coef, R4, R4, dst=0) if dist is not None else coef
+    barrier()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    ev[0].record()
+    run_ptm()
+    ev[1].record()
+    full = sharding.gather_planar(coef, R4, R4, dst=0) if dist is not None else coef
+    ev[2].record()
+    barrier()
+    t = torch.tensor([ev[0].elapsed_time(ev[1]), ev[1].elapsed_time(ev[2]), ev[0].elapsed_time(ev[2])],
+                     dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ptm_ms, gather_ms, total_ms = [float(v) for v in t.tolist()]
+    nbad = int(bad.sum().item())
+    # sampled oracle check: coefficients anywhere in the slab, table columns in the last sub-slab
+    rng = np.random.default_rng(7 + rank)
+    last0 = ((nr - 1) // SUB) * SUB
+    last_rows = nr - last0
+    idx_c = rng.integers(0, P_loc, 6)
+    idx_t = rng.integers(0, last_rows * R4, 6)
+    fl = frames.view(N4, P_loc)
+    par_c = parity_sample(lambda y, x: fl[:, y * R4 + x].cpu().numpy(), cams, r0, R4, P_loc,
+                          coef[:, torch.from_numpy(idx_c).cuda()].cpu().numpy(), None, idx_c)
+    par_t = parity_sample(lambda y, x: fl[:, (last0 + y) * R4 + x].cpu().numpy(), cams, r0 + last0, R4,
+                          last_rows * R4, None, table[:, torch.from_numpy(idx_t).cuda()].cpu().numpy(), idx_t)
+    par = torch.tensor([par_c["max_rel"], float(par_t["table_mismatch"]), float(nbad)], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(par, op=dist.ReduceOp.MAX)
+    if rank == 0 and dist is not None:
+        # the gathered map must hold rank 0's own slab bit for bit
+        assert torch.equal(full[:, r0:r0 + nr, :].reshape(6, -1), coef)
+    P = R4 * R4
+    alg = (N4 + 48 + 4 * G * G) * P
+    gather_bytes = 48 * (P - P_loc) if world > 1 else 0
+    out = {"workload": "synthetic 4096x4096 ROI x 1000 light samples, PTM fit + 100x100 light grid (BASELINE configs[3])",
+           "scaling": "strong", "ranks": world, "rows_per_rank": nr, "sub_slab_rows": SUB,
+           "ptm_ms": ptm_ms, "gather_ms": gather_ms, "total_ms": total_ms,
+           "value": P * N4 / (total_ms * 1e-3) / 1e6, "unit": UNIT,
+           "nccl_gather_bytes": gather_bytes,
+           "nccl_gather_gbs": (gather_bytes / (gather_ms * 1e-3) / 1e9) if world > 1 else None,
+           "gather": "fp64 coefficient map (6, rows, cols) to rank 0, sharding.gather_planar (batch_isend_irecv)",
+           "roofline": {"bound": "hbm", "achieved": alg / world / (ptm_ms * 1e-3) / 1e9, "peak": hbm_peak,
+                        "frac": alg / world / (ptm_ms * 1e-3) / 1e9 / hbm_peak, "unit": "GB/s per GPU"},
+           "parity_sample": {"pixels_per_rank": 12, "max_rel": float(par[0].item()),
+                             "table_mismatch": int(par[1].item()), "singular": int(par[2].item())}}
+    del frames, coef, table, full
+    torch.cuda.empty_cache()
+    return out
+
+
 # ------------------------------------------------------------------------------ GPU arm
 def run_gpu(args, rank, local_rank, world):
     import torch
     import rti_b200
     from rti_b200 import _capi, synthetic
 
-    cpu = None
+    cpu = cpu_rbf = None
     if world == 1 and not args.no_cpu_baseline:       # before CUDA is initialised: the pool forks
-        v, cores, sample, _ = cpu_reference(args.cpu_pixels_per_core)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        cpu, _ = cpu_reference(args.cpu_pixels_per_core)
+        cpu_rbf, _ = cpu_reference(max(args.cpu_pixels_per_core // 12, 1), mode="rbf")
 
     torch.cuda.set_device(local_rank)
     dist = None
@@ -345,11 +516,19 @@ def run_gpu(args, rank, local_rank, world):
     ms_per_step = total_ms / args.steps
     value = units_per_rank * world / (ms_per_step * 1e-3) / 1e6
 
+    # ---- sampled oracle check of what the timed steps left in HBM (coefficients + table columns)
+    rng = np.random.default_rng(11 + rank)
+    idx = rng.integers(0, p, args.parity_pixels)
+    d_idx = torch.from_numpy(idx).cuda()
+    parity = parity_sample(lambda y, x: frames[:, y, x], cams, row0, COLS, p,
+                           d_coef[:, d_idx].cpu().numpy(), d_table.view(G * G, p)[:, d_idx].cpu().numpy(), idx)
+    parity["singular"] = int(d_bad.sum().item())
+
     # ---- e2e: the host-buffer C-ABI call, H2D of the frames and D2H of the table inside
     e2e = None
     table_bytes = G * G * p * 4
     if not args.no_e2e:
-        del d_table
+        d_table = None
         torch.cuda.empty_cache()
         try:
             import psutil
@@ -385,10 +564,47 @@ def run_gpu(args, rank, local_rank, world):
                    "d2h_bytes_per_step": int(table_bytes), "ms_per_step": dt * 1e3, "steps": args.e2e_steps,
                    "api": "rti_ptm_compute_host (pinned host frames -> int32 table in pinned host memory)"}
             lib.rti_destroy()
+            # the host table of the last e2e step against the oracle (the host call numbers rows from 0)
+            hp = parity_sample(lambda y, x: frames[:, y, x], cams, 0, COLS, p, None,
+                               h_table.view(G * G, p)[:, torch.from_numpy(idx)].numpy(), idx)
+            e2e["parity_sample"] = {"pixels": hp["pixels"], "table_mismatch": hp["table_mismatch"],
+                                    "table_integer_boundary_flips": hp["table_integer_boundary_flips"]}
+            # ---- e2e roofline: the same D2H bytes as bare pinned copies (4 GiB pieces of a device
+            # buffer into consecutive parts of the pinned table), all ranks at the same time
+            piece = min(1 << 32, table_bytes)
+            d_src = torch.empty(piece, dtype=torch.uint8, device="cuda")
+            h_flat = h_table.view(torch.uint8).view(-1)
+            barrier()
+            t0 = time.perf_counter()
+            off = 0
+            while off < table_bytes:
+                nb = min(piece, table_bytes - off)
+                h_flat[off:off + nb].copy_(d_src[:nb], non_blocking=True)
+                off += nb
+            torch.cuda.synchronize()
+            bare = time.perf_counter() - t0
+            if dist is not None:
+                t = torch.tensor([bare], dtype=torch.float64, device="cuda")
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                bare = float(t.item())
+            e2e["roofline"] = {"bound": "pcie d2h", "what": "bare cudaMemcpyAsync of the step's D2H bytes into the same "
+                               "pinned buffer, %d rank(s) concurrently" % world,
+                               "bare_copy_ms": bare * 1e3, "bare_copy_gbs_per_rank": table_bytes / bare / 1e9,
+                               "bare_copy_gbs_aggregate": world * table_bytes / bare / 1e9,
+                               "e2e_gbs_per_rank": table_bytes / dt / 1e9, "frac": bare / dt}
+            del d_src, h_table
 
     secondary = None
     if world == 1 and not args.no_secondary:
         secondary = secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p)
+        if cpu_rbf is not None:
+            secondary["rbf_per_pixel_lights"]["cpu_baseline"] = cpu_rbf
+            secondary["rbf_per_pixel_lights"]["vs_cpu"] = secondary["rbf_per_pixel_lights"]["value"] / cpu_rbf["value"]
+    config4 = None
+    if not args.no_config4:
+        d_table = d_coef = d_frames = None                          # release the headline buffers
+        torch.cuda.empty_cache()
+        config4 = config4_strong(torch, dist, _capi, lib, rank, world, read_peaks()[0])
 
     if rank != 0:
         return
@@ -413,12 +629,10 @@ def run_gpu(args, rank, local_rank, world):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "rows_per_gpu": ROWS, "cols": COLS, "lights": N_LIGHTS,
-                   "grid": [G, G], "parallelism": "row-tile x%d, no collective" % world,
-                   "l2": "inputs (524 MB) and the 42 GB table written per step exceed the 126 MB L2"},
-        "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
+        "config": make_config(world),
+        "e2e": e2e, "parity_sample": parity, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "kernel_ms": {"ptm_fused": fused_ms, "ptm_fit_frames": fit_ms, "ptm_table": table_ms},
-        "secondary": secondary,
+        "secondary": secondary, "config4": config4,
     }
     return line
 
@@ -433,6 +647,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the linear-RBF side measurements")
+    ap.add_argument("--no-config4", action="store_true", help="skip the strong-scaled BASELINE configs[3] run")
+    ap.add_argument("--parity-pixels", type=int, default=64)
     ap.add_argument("--cpu-pixels-per-core", type=int, default=96)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "native" else args.warmup

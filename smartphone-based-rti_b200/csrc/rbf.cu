@@ -522,6 +522,107 @@ rbf_eval_kernel(const float *__restrict__ lx, const float *__restrict__ ly, cons
     if (any_bad && bad != nullptr) atomicAdd(bad, 1);
 }
 
+// --------------------------------------------------------------------------------------
+// Grid evaluation with float32 distances (rti_rbf_table_fast).  The north star allows 1e-3 on
+// RBF grid values; the fp64 kernel above delivers 1e-8 and is bound by the fp64 pipe.  Here the
+// distance |g - n_k| is formed in float32 (one FADD, one FFMA, one MUFU.SQRT: relative error
+// ~1e-7) and only the product with the weight and the running sum stay in fp64 (one DFMA):
+// the weights of a linear RBF are large and cancel (sum |w_k| ~ 1e6 for values ~ 1e2 at
+// N = 500), so rounding THEM or the partial sums to float32 costs 1e-3 of the result while a
+// 1e-7 relative error on each distance costs ~1e-5.  The float32 -> fp64 widening of r >= 0 is
+// done with two shifts and an add on the integer pipe (exponent re-bias 127 -> 1023) because
+// F2F.F64.F32 shares the XU pipe with MUFU, which is the unit this kernel is bound by:
+// G*G*N square roots per pixel at 16 per clock per SM.
+// A CTA owns PB consecutive pixels; a thread owns FE_U consecutive directions of one grid row.
+// --------------------------------------------------------------------------------------
+constexpr int FE_KCH = 128;             // nodes staged per chunk
+
+__device__ __forceinline__ double widen_pos_f32(float r) {
+    const uint32_t b = __float_as_uint(r);
+    return __hiloint2double((int)((b >> 3) + 0x38000000u), (int)(b << 29));   // r = 0 maps to 2^-127
+}
+
+template <int PB, int FE_U>
+__global__ void __launch_bounds__(EV_THREADS)
+rbf_eval_f32_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const double *__restrict__ weights,
+                    int64_t n_pixels, int n, const double *__restrict__ axis, int g, int strips_per_row,
+                    int32_t *__restrict__ out, int64_t image_stride, int32_t *__restrict__ bad) {
+    __shared__ float2 s_xy[PB][FE_KCH];
+    __shared__ double s_w[PB][FE_KCH];
+    const int64_t p0 = (int64_t)blockIdx.x * PB;
+    const int strip = blockIdx.y * EV_THREADS + threadIdx.x;
+    const bool live = strip < strips_per_row * g;
+    const int v = live ? strip / strips_per_row : 0;
+    const int u0 = live ? (strip - v * strips_per_row) * FE_U : 0;
+    float gx[FE_U];
+#pragma unroll
+    for (int j = 0; j < FE_U; ++j) gx[j] = (float)axis[min(u0 + j, g - 1)];
+    const float gy = (float)axis[v];
+    double acc[PB][FE_U];
+#pragma unroll
+    for (int q = 0; q < PB; ++q)
+#pragma unroll
+        for (int j = 0; j < FE_U; ++j) acc[q][j] = 0.0;
+
+    for (int k0 = 0; k0 < n; k0 += FE_KCH) {
+        const int kc = min(FE_KCH, n - k0);
+        __syncthreads();
+        for (int e = threadIdx.x; e < PB * kc; e += EV_THREADS) {
+            const int q = e / kc, k = e - q * kc;
+            const int64_t p = (p0 + q < n_pixels) ? p0 + q : n_pixels - 1;
+            s_xy[q][k] = make_float2(lx[p * n + k0 + k], ly[p * n + k0 + k]);
+            s_w[q][k] = weights[p * n + k0 + k];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < PB; ++q) {
+#pragma unroll 2
+            for (int k = 0; k < kc; ++k) {
+                const float2 xy = s_xy[q][k];
+                const double wk = s_w[q][k];
+                const float dy = gy - xy.y;
+                const float dy2 = dy * dy;
+#pragma unroll
+                for (int j = 0; j < FE_U; ++j) {
+                    const float dx = gx[j] - xy.x;
+                    float r;
+                    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(dx, dx, dy2)));
+                    acc[q][j] = fma(widen_pos_f32(r), wk, acc[q][j]);
+                }
+            }
+        }
+    }
+    if (!live) return;
+    bool any_bad = false;
+#pragma unroll
+    for (int j = 0; j < FE_U; ++j) {
+        if (u0 + j >= g) break;
+        const int64_t d = (int64_t)v * g + u0 + j;
+        int32_t *dst = out + d * image_stride + p0;
+        if (PB % 4 == 0 && p0 + PB <= n_pixels && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+#pragma unroll
+            for (int q = 0; q < PB; q += 4) {
+                int val[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    if (!(fabs(acc[q + i][j]) < 2147483648.0)) any_bad = true;
+                    val[i] = trunc_i32(acc[q + i][j]);
+                }
+                __stcs(reinterpret_cast<int4 *>(dst + q), make_int4(val[0], val[1], val[2], val[3]));
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < PB; ++q) {
+                if (p0 + q < n_pixels) {
+                    if (!(fabs(acc[q][j]) < 2147483648.0)) any_bad = true;
+                    dst[q] = trunc_i32(acc[q][j]);
+                }
+            }
+        }
+    }
+    if (any_bad && bad != nullptr) atomicAdd(bad, 1);
+}
+
 }  // namespace rti
 
 using namespace rti;
@@ -593,4 +694,28 @@ extern "C" int rti_rbf_grids(const float *d_lx, const float *d_ly, const double 
                              const double *d_axis, int g, double *d_grids, rti_stream_t stream) {
     return rbf_eval_launch<false>(d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_grids, 0, nullptr, stream,
                                   "rti_rbf_grids");
+}
+
+#ifndef RTI_FE_PB
+#define RTI_FE_PB 8
+#endif
+#ifndef RTI_FE_U
+#define RTI_FE_U 4
+#endif
+extern "C" int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels,
+                                  int n, const double *d_axis, int g, int32_t *d_table, int64_t image_stride,
+                                  int32_t *d_bad, rti_stream_t stream) {
+    const char *who = "rti_rbf_table_fast";
+    RTI_REQUIRE(d_lx && d_ly && d_weights && d_axis && d_table, "%s: NULL pointer", who);
+    RTI_REQUIRE(n_pixels > 0 && n > 0 && g > 0 && g <= 2048, "%s: bad sizes", who);
+    RTI_REQUIRE(image_stride >= n_pixels, "%s: image_stride < pixels", who);
+    constexpr int PB = RTI_FE_PB, U = RTI_FE_U;
+    const int strips_per_row = (g + U - 1) / U;
+    const unsigned gy = (unsigned)(((int64_t)strips_per_row * g + EV_THREADS - 1) / EV_THREADS);
+    const int64_t bx = (n_pixels + PB - 1) / PB;
+    RTI_REQUIRE(bx <= 0x7fffffffLL, "%s: too many pixels", who);
+    rbf_eval_f32_kernel<PB, U><<<dim3((unsigned)bx, gy), EV_THREADS, 0, as_stream(stream)>>>(
+        d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, strips_per_row, d_table, image_stride, d_bad);
+    RTI_LAUNCHED("rbf_eval_f32_kernel");
+    return RTI_OK;
 }

@@ -30,8 +30,11 @@ def gather_planar(local, rows_total: int, cols: int, dst: int = 0, group=None):
     """Gather per-rank planar maps (K, rows_r * cols) into (K, rows_total, cols) on `dst`.
 
     `local` is this rank's tensor for its row_partition() slab (any K, any dtype, CPU or
-    CUDA).  Point-to-point sends (uneven slabs need no padding); returns the assembled
-    tensor on `dst` and None elsewhere.
+    CUDA).  One batch of point-to-point operations (`batch_isend_irecv`: a single NCCL group
+    on GPUs, so all sources stream to `dst` concurrently over NVLink): every rank sends its K
+    planes, `dst` receives each plane slab straight into its place in the assembled tensor
+    (a plane's row slab is contiguous there, so there is no staging copy and uneven slabs need
+    no padding).  Returns the assembled tensor on `dst` and None elsewhere.
     """
     import torch
     import torch.distributed as dist
@@ -43,20 +46,24 @@ def gather_planar(local, rows_total: int, cols: int, dst: int = 0, group=None):
     r0, nr = parts[rank]
     if local.shape != (k, nr * cols):
         raise ValueError("rank %d: expected local shape %s, got %s" % (rank, (k, nr * cols), tuple(local.shape)))
+    local = local.contiguous()
+    ops = []
+    full = None
     if rank != dst:
         if nr > 0:
-            dist.send(local.contiguous(), dst=dst, group=group)
-        return None
-    full = torch.empty((k, rows_total, cols), dtype=local.dtype, device=local.device)
-    for src, (s0, sn) in enumerate(parts):
-        if sn == 0:
-            continue
-        if src == dst:
-            full[:, s0:s0 + sn, :] = local.view(k, sn, cols)
-        else:
-            buf = torch.empty((k, sn * cols), dtype=local.dtype, device=local.device)
-            dist.recv(buf, src=src, group=group)
-            full[:, s0:s0 + sn, :] = buf.view(k, sn, cols)
+            ops = [dist.P2POp(dist.isend, local[i], dst, group) for i in range(k)]
+    else:
+        full = torch.empty((k, rows_total, cols), dtype=local.dtype, device=local.device)
+        for src, (s0, sn) in enumerate(parts):
+            if sn == 0:
+                continue
+            if src == dst:
+                full[:, s0:s0 + sn, :] = local.view(k, sn, cols)
+            else:
+                ops += [dist.P2POp(dist.irecv, full[i, s0:s0 + sn, :].view(-1), src, group) for i in range(k)]
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
     return full
 
 
