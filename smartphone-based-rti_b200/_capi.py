@@ -62,6 +62,7 @@ SIGNATURES = {
     "rti_rbf_workspace_bytes": (_l, [_i, _i]),
     "rti_rbf_fit_soa": (_i, [_p, _p, _p, _l, _i, _p, _p, _l, _i, _p, _p]),
     "rti_rbf_table": (_i, [_p, _p, _p, _l, _i, _p, _i, _p, _l, _p, _p]),
+    "rti_rbf_table_fast": (_i, [_p, _p, _p, _l, _i, _p, _i, _p, _l, _p, _p]),
     "rti_rbf_grids": (_i, [_p, _p, _p, _l, _i, _p, _i, _p, _p]),
     "rti_rbf_shared_operator_elems": (_l, [_i, _i]),
     "rti_rbf_shared_packed_elems": (_l, [_i, _l]),

@@ -16,75 +16,9 @@
 // is one contiguous cp.async stream into shared memory.  The two right-hand sides ride
 // along as two extra rows of the matrix, which performs the forward substitution inside
 // the factorisation; only the backward substitution remains.
-#include "common.cuh"
+#include "rbf_tiles.cuh"
 
 namespace rti {
-
-constexpr int TS = 64;                  // tile edge
-constexpr int KC = 32;                  // k-rows per 16 KB block of the L workspace
-constexpr int BLK = KC * TS;            // doubles per block (16 KB)
-constexpr int KS = 16;                  // k-rows staged per pipeline stage
-constexpr int LDS = TS + 4;             // leading dimension of staged operands: the 4 k-rows of a DMMA
-                                        // fragment land in disjoint bank groups (68*2 mod 32 = 8)
-constexpr int STG = KS * LDS;           // doubles per staged operand chunk
-constexpr int RBF_THREADS = 256;
-constexpr int SD_LD = TS + 1;           // padded leading dimension of the potrf scratch
-
-__host__ __device__ inline int rbf_mpad(int n) { return ((n - 1 + 2 + TS - 1) / TS) * TS; }
-
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem) {
-    const unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
-
-// |d| for d2 >= 0 in fp64 (MUFU seed + Newton, ~2 ulp); 0 for d2 == 0
-__device__ __forceinline__ double sqrt_pos(double d2) { return d2 > 0.0 ? d2 * rsqrt_pos(d2) : 0.0; }
-
-// fp64 tensor-core step: D(8x8) += A(8x4) . B(4x8), mma.sync.m8n8k4 (DMMA).  Lane l holds
-// A[l>>2][l&3], B[l&3][l>>2] and D[l>>2][2*(l&3) + {0,1}].  Measured on B200: 18.5 T FMA/s
-// against 16.8 T for DFMA chains (tools/peak_fp64.cu), with 1/8 of the issue slots and 1/8 of
-// the shared-memory operand traffic of a 4x4 register-tiled DFMA micro-kernel.
-__device__ __forceinline__ void dmma(double &c0, double &c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
-
-// A warp owns a 16 x 32 patch of the 64 x 64 tile: 2 x 4 DMMA tiles, acc[mi][ni][e] is element
-// (rw + 8*mi + (lane>>2), cw + 8*ni + 2*(lane&3) + e).
-// acc -= sum_k A[k][row] * B[k][col] over `depth` staged k-rows (operands [k][LD], k-major).
-template <int LD>
-__device__ __forceinline__ void mma_chunk(double (&acc)[2][4][2], const double *__restrict__ sA,
-                                          const double *__restrict__ sB, int rw, int cw, int lane, int depth) {
-    const double *pa = sA + (lane & 3) * LD + rw + (lane >> 2);
-    const double *pb = sB + (lane & 3) * LD + cw + (lane >> 2);
-#pragma unroll 4
-    for (int k = 0; k < depth; k += 4) {
-        double a[2], b[4];
-#pragma unroll
-        for (int mi = 0; mi < 2; ++mi) a[mi] = -pa[k * LD + 8 * mi];
-#pragma unroll
-        for (int ni = 0; ni < 4; ++ni) b[ni] = pb[k * LD + 8 * ni];
-#pragma unroll
-        for (int mi = 0; mi < 2; ++mi)
-#pragma unroll
-            for (int ni = 0; ni < 4; ++ni) dmma(acc[mi][ni][0], acc[mi][ni][1], a[mi], b[ni]);
-    }
-}
-
-__device__ __forceinline__ double block_sum(double v, double *s_red) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    __syncthreads();
-    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = v;
-    __syncthreads();
-    double t = 0.0;
-#pragma unroll
-    for (int w = 0; w < RBF_THREADS / 32; ++w) t += s_red[w];
-    return t;
-}
 
 // Shared memory map (doubles):  [0, 2*STG) sA (2 stages)   [2*STG, 4*STG) sB (2 stages)
 //   the potrf scratch sD[64][65] and the transposed C tile sCk[64][LDS] alias sA/sB, as do the
@@ -696,20 +630,10 @@ extern "C" int rti_rbf_grids(const float *d_lx, const float *d_ly, const double 
                                   "rti_rbf_grids");
 }
 
-#ifndef RTI_FE_PB
-#define RTI_FE_PB 8
-#endif
-#ifndef RTI_FE_U
-#define RTI_FE_U 4
-#endif
-extern "C" int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels,
-                                  int n, const double *d_axis, int g, int32_t *d_table, int64_t image_stride,
-                                  int32_t *d_bad, rti_stream_t stream) {
-    const char *who = "rti_rbf_table_fast";
-    RTI_REQUIRE(d_lx && d_ly && d_weights && d_axis && d_table, "%s: NULL pointer", who);
-    RTI_REQUIRE(n_pixels > 0 && n > 0 && g > 0 && g <= 2048, "%s: bad sizes", who);
-    RTI_REQUIRE(image_stride >= n_pixels, "%s: image_stride < pixels", who);
-    constexpr int PB = RTI_FE_PB, U = RTI_FE_U;
+template <int PB, int U>
+static int rbf_fast_launch(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels, int n,
+                           const double *d_axis, int g, int32_t *d_table, int64_t image_stride, int32_t *d_bad,
+                           rti_stream_t stream, const char *who) {
     const int strips_per_row = (g + U - 1) / U;
     const unsigned gy = (unsigned)(((int64_t)strips_per_row * g + EV_THREADS - 1) / EV_THREADS);
     const int64_t bx = (n_pixels + PB - 1) / PB;
@@ -718,4 +642,24 @@ extern "C" int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const do
         d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, strips_per_row, d_table, image_stride, d_bad);
     RTI_LAUNCHED("rbf_eval_f32_kernel");
     return RTI_OK;
+}
+
+extern "C" int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels,
+                                  int n, const double *d_axis, int g, int32_t *d_table, int64_t image_stride,
+                                  int32_t *d_bad, rti_stream_t stream) {
+    const char *who = "rti_rbf_table_fast";
+    RTI_REQUIRE(d_lx && d_ly && d_weights && d_axis && d_table, "%s: NULL pointer", who);
+    RTI_REQUIRE(n_pixels > 0 && n > 0 && g > 0 && g <= 2048, "%s: bad sizes", who);
+    RTI_REQUIRE(image_stride >= n_pixels, "%s: image_stride < pixels", who);
+#define RTI_FAST_ARGS d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_table, image_stride, d_bad, stream, who
+    static const int variant = getenv("RTI_RBF_FAST_VARIANT") ? atoi(getenv("RTI_RBF_FAST_VARIANT")) : 0;
+    // development A/B (tools/prof_rbf.py, N = 500, 4736 pixels): <8,4> 6.94 ms, <4,10> 7.14, <8,5> 6.84,
+    // <2,10> 6.62, <4,4> 6.55 ms = 0.78 of the SFU peak (ncu: XU pipe 80 %, issue slots 76 %, stalls = MIO
+    // throttle, i.e. the MUFU queue is full); 0 is the shipped shape
+    switch (variant) {
+    case 1: return rbf_fast_launch<8, 4>(RTI_FAST_ARGS);
+    case 2: return rbf_fast_launch<2, 10>(RTI_FAST_ARGS);
+    default: return rbf_fast_launch<4, 4>(RTI_FAST_ARGS);
+    }
+#undef RTI_FAST_ARGS
 }

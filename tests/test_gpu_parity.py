@@ -634,6 +634,40 @@ def test_rbf_fit_and_eval_n1000_vs_oracle(torch_cuda):
         assert np.count_nonzero(diff) <= 2
 
 
+RBF_FAST_RTOL = 5e-4       # float32 distances, fp64 weights and sums: ~5e-5 typical, 2e-4 worst on white-noise
+                           # intensities at N = 500; north_star allows 1e-3 of the grid value
+
+
+@pytest.mark.parametrize("p,n", [(13, 40), (8, 300), (19, 500), (4, 1000)])
+def test_rbf_table_fast_vs_oracle(torch_cuda, p, n):
+    """rti_rbf_table_fast (float32 node distances) against scipy's fp64 evaluation (analysis.py:259-260,
+    :400-409): every table entry within RBF_FAST_RTOL * max|grid| + 1 of trunc(oracle), and equal to it
+    wherever the fp64 value is farther than that from an integer."""
+    from rti_b200 import _capi
+    torch = torch_cuda
+    lx, ly, inten = random_nodes(p, n, seed=77 + n)
+    w, bad, (d_lx, d_ly) = gpu_rbf_fit(torch, lx, ly, inten)
+    assert bad == 0
+    ax = orc.light_axis()
+    d_ax = dev(torch, ax)
+    stride = p + 3                                        # padded image stride, odd pixel count
+    table = torch.full((100, 100, stride), -7, dtype=torch.int32, device="cuda")
+    tb = torch.zeros(1, dtype=torch.int32, device="cuda")
+    _capi.call("rti_rbf_table_fast", d_lx.data_ptr(), d_ly.data_ptr(), w.data_ptr(), p, n, d_ax.data_ptr(), 100,
+               table.data_ptr(), stride, tb.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert int(tb.item()) == 0
+    tab = table.cpu().numpy()
+    assert np.all(tab[:, :, p:] == -7)                    # nothing written past the pixels
+    for i in range(p):
+        ref = orc.rbf_grid(lx[i], ly[i], orc.rbf_fit(lx[i], ly[i], inten[i]), ax)
+        tol = RBF_FAST_RTOL * np.max(np.abs(ref))
+        exact = np.trunc(ref).astype(np.int32)
+        diff = tab[:, :, i] != exact
+        assert np.all(np.abs(tab[:, :, i] - exact) <= 1)
+        assert np.all(np.abs(ref[diff] - np.rint(ref[diff])) <= tol)
+
+
 def test_rbf_reference_golden_grids_and_table(torch_cuda, ref_small, ref_rbf_n96):
     from rti_b200 import _capi
     torch = torch_cuda

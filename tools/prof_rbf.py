@@ -24,6 +24,7 @@ def main():
     ap.add_argument("--reps", type=int, default=1)
     ap.add_argument("--batch", type=int, default=148 * 2)
     ap.add_argument("--no-eval", action="store_true")
+    ap.add_argument("--fast", action="store_true", help="also time rti_rbf_table_fast (float32 distances)")
     args = ap.parse_args()
     torch.cuda.set_device(0)
     lib = _capi.load()
@@ -54,6 +55,17 @@ def main():
         torch.cuda.synchronize()
         print("n=%d pixels=%d fit %.3f ms (%.0f px/s)  table %.3f ms  bad=%d"
               % (n, px, a.elapsed_time(b), px / a.elapsed_time(b) * 1e3, b.elapsed_time(c), int(bad.item())))
+        if args.fast:
+            d, e = (torch.cuda.Event(enable_timing=True) for _ in range(2))
+            d.record()
+            _capi.call("rti_rbf_table_fast", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), px, n, axis.data_ptr(), 100,
+                       tab.data_ptr(), px, bad.data_ptr(), S)
+            e.record()
+            torch.cuda.synchronize()
+            ms = d.elapsed_time(e)
+            sm_clk = 148 * 16 * 1.965e9
+            print("   table_fast %.3f ms: %.3f us/pixel, %.2f Tsqrt/s = %.2f of the SFU peak (148 SM x 16/clk x 1.965 GHz)"
+                  % (ms, ms * 1e3 / px, 1e4 * n * px / ms / 1e9, 1e4 * n * px / (ms * 1e-3) / sm_clk))
 
 
 if __name__ == "__main__":
