@@ -162,6 +162,23 @@ int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten
                     int64_t n_pixels, int n, double *d_weights,
                     void *d_work, int64_t work_bytes, int batch,
                     int32_t *d_bad, rti_stream_t stream);
+/* The same fit, tile-preconditioned (rbf_pcg.cu): the SoA arrays describe a rows x cols slab
+ * (pixel = y*cols + x).  Per 16x16 pixel tile the reduced matrix of the tile-centre pixel is
+ * inverted once in fp64 and serves as the preconditioner of conjugate-gradient solves of every
+ * pixel of the tile; matrix entries are regenerated per step in float32 and accumulated in
+ * fp64, the preconditioner is applied to all pixels by one batched tcgen05 contraction per
+ * step.  Weights reproduce the node values to ~tol (absolute, in intensity units; e.g. 0.01)
+ * and scipy's grid values to ~1e-4 of their maximum (north_star allows 1e-3).
+ * d_work: rti_rbf_pcg_workspace_bytes(n, tiles) bytes for `tiles` tiles in flight (>= 1; the
+ * call batches the slab's tiles through whatever it is given), 256-byte aligned.
+ * d_iters: optional int32 [rows*cols], steps each pixel took.  d_bad: int32[2]; [0] counts
+ * tiles whose centre matrix is singular (duplicate nodes), [1] pixels that did not reach tol
+ * within max_iters steps -- refit those with rti_rbf_fit_soa.  3 <= n <= 1025. */
+int64_t rti_rbf_pcg_workspace_bytes(int n, int64_t tiles);
+int rti_rbf_fit_pcg(const float *d_lx, const float *d_ly, const int32_t *d_inten,
+                    int rows, int cols, int n, double *d_weights,
+                    void *d_work, int64_t work_bytes, int max_iters, double tol,
+                    int32_t *d_iters, int32_t *d_bad, rti_stream_t stream);
 /* Rbf.__call__ on the grid: value(v,u) = sum_k ||(axis[u], axis[v]) - n_k|| w_k.
  * Table layout / truncation / d_bad as rti_ptm_table. */
 int rti_rbf_table(const float *d_lx, const float *d_ly, const double *d_weights,

@@ -96,6 +96,12 @@ struct GemmArgs {
     double *out_f64;           // MODE 2: float64 [P][R] (pixel-major)
     int32_t *bad;              // pixels x rows whose value does not fit int32 (MODE 0/1)
     int num_m_blks, num_n_blks;
+    // batched form (rbf_pcg.cu: one preconditioner per pixel tile): pixel block n_blk uses operator
+    // n_blk / blks_per_op, whose rows start at that index times op_row_stride in the operator arrays and
+    // in inv_scale; the operator's K extent wraps after a_num_k stages (B = [r_hi; r_lo] stacked along K
+    // against one copy of the operator); tile_active[op] == 0 skips the operator's pixel blocks.
+    int a_num_k, blks_per_op, op_row_stride;
+    const int32_t *tile_active;
 };
 
 enum { STORE_TMA = 0, STORE_DIRECT = 1, STORE_F64_PIXEL_MAJOR = 2 };
@@ -151,13 +157,17 @@ rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int m_blk = tile % args.num_m_blks, n_blk = tile / args.num_m_blks;
+                const int op = n_blk / args.blks_per_op;
+                if (args.tile_active != nullptr && args.tile_active[op] == 0) continue;
+                const int a_row = op * args.op_row_stride + m_blk * BM;
                 for (int kb = 0; kb < num_k; ++kb) {
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                     const uint32_t full = bar_full + 8 * stage;
                     const uint32_t sa = base + stage * STAGE_BYTES;
+                    const int a_col = (kb % args.a_num_k) * BK;
                     mbar_expect_tx(full, STAGE_BYTES);
-                    tma_load_2d(sa, &map_hi, kb * BK, m_blk * BM, full);
-                    tma_load_2d(sa + A_TILE, &map_lo, kb * BK, m_blk * BM, full);
+                    tma_load_2d(sa, &map_hi, a_col, a_row, full);
+                    tma_load_2d(sa + A_TILE, &map_lo, a_col, a_row, full);
 #pragma unroll
                     for (int j = 0; j < BN / 64; ++j)
                         tma_load_3d(sa + 2 * A_TILE + j * B_BOX, &map_b, j * 64, kb * BK, n_blk, full);
@@ -171,6 +181,8 @@ rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_
             int stage = 0, acc = 0;
             uint32_t phase = 0, aphase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+                if (args.tile_active != nullptr &&
+                    args.tile_active[(tile / args.num_m_blks) / args.blks_per_op] == 0) continue;
                 mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
@@ -206,9 +218,11 @@ rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_
         int chunk_parity = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
             const int m_blk = tile % args.num_m_blks, n_blk = tile / args.num_m_blks;
+            const int op = n_blk / args.blks_per_op;
+            if (args.tile_active != nullptr && args.tile_active[op] == 0) continue;
             const int row = m_blk * BM + q * 32 + lane;
             const bool row_ok = row < args.op_rows;
-            const float sc = row_ok ? __ldg(args.inv_scale + row) : 0.0f;
+            const float sc = row_ok ? __ldg(args.inv_scale + (long long)op * args.op_row_stride + row) : 0.0f;
             mbar_wait(bar_tfull + 8 * acc, aphase);
             tc_fence_after();
 #pragma unroll 1
@@ -457,6 +471,10 @@ int gemm_launch(const uint16_t *d_packed, int n, long long n_pixels, const uint1
     args.bad = d_bad;
     args.num_m_blks = (int)(r_pad / BM);
     args.num_n_blks = (int)((n_pixels + BN - 1) / BN);
+    args.a_num_k = (int)(n_pad / BK);
+    args.blks_per_op = 0x7fffffff;
+    args.op_row_stride = 0;
+    args.tile_active = nullptr;
     int dev = 0, sms = 148;
     RTI_CUDA(cudaGetDevice(&dev));
     RTI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -478,6 +496,54 @@ int gemm_launch(const uint16_t *d_packed, int n, long long n_pixels, const uint1
 }
 
 }  // namespace
+
+// Batched contraction for the tile-preconditioned conjugate gradients of rbf_pcg.cu:
+//   out[col][0:op_rows_pad] = (op_hi + op_lo)[col / (blks_per_op*256)] . ([B_hi; B_lo])[:, col]
+// d_packed: fp16 [n_cols/256][k_rows][256] with k_rows = 2 * a_k_pad (hi rows then lo rows of the
+// vector operand); operators: fp16 [n_ops][op_rows_pad][a_k_pad]; out float64 [n_cols][op_rows_pad].
+int rbf_gemm_batched(const uint16_t *d_packed, int k_rows, long long n_cols, const uint16_t *d_op_hi,
+                     const uint16_t *d_op_lo, const float *d_inv_scale, int n_ops, int op_rows_pad, int a_k_pad,
+                     int blks_per_op, double *d_out, const int32_t *d_tile_active, cudaStream_t stream) {
+    RTI_REQUIRE(op_rows_pad % BM == 0 && a_k_pad % BK == 0 && k_rows % BK == 0 && n_cols % BN == 0,
+                "rbf_gemm_batched: unpadded shape");
+    CUtensorMap map_hi, map_lo, map_b;
+    int rc;
+    const uint64_t rows_all = (uint64_t)n_ops * op_rows_pad;
+    if ((rc = make_map_2d(&map_hi, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, d_op_hi, a_k_pad, rows_all, (uint64_t)a_k_pad * 2, BK, BM,
+                          "pcg op_hi")))
+        return rc;
+    if ((rc = make_map_2d(&map_lo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, d_op_lo, a_k_pad, rows_all, (uint64_t)a_k_pad * 2, BK, BM,
+                          "pcg op_lo")))
+        return rc;
+    if ((rc = make_map_packed(&map_b, d_packed, k_rows, n_cols / BN))) return rc;
+    GemmArgs args;
+    args.op_rows = op_rows_pad;
+    args.n = k_rows;
+    args.n_pixels = n_cols;
+    args.inv_scale = d_inv_scale;
+    args.table = nullptr;
+    args.image_stride = 0;
+    args.out_f64 = d_out;
+    args.bad = nullptr;
+    args.num_m_blks = op_rows_pad / BM;
+    args.num_n_blks = (int)(n_cols / BN);
+    args.a_num_k = a_k_pad / BK;
+    args.blks_per_op = blks_per_op;
+    args.op_row_stride = op_rows_pad;
+    args.tile_active = d_tile_active;
+    int dev = 0, sms = 148;
+    RTI_CUDA(cudaGetDevice(&dev));
+    RTI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const long long tiles = (long long)args.num_m_blks * args.num_n_blks;
+    RTI_REQUIRE(tiles < (1ll << 31), "rbf_gemm_batched: too many tiles");
+    const int grid = (int)(tiles < sms ? tiles : sms);
+    RTI_CUDA(cudaFuncSetAttribute(rbf_shared_gemm_kernel<STORE_F64_PIXEL_MAJOR>,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
+    rbf_shared_gemm_kernel<STORE_F64_PIXEL_MAJOR><<<grid, THREADS, SMEM_BYTES, stream>>>(map_hi, map_lo, map_b, map_b, args);
+    RTI_LAUNCHED("rbf_shared_gemm_kernel");
+    return RTI_OK;
+}
+
 }  // namespace rti
 
 // ---- C ABI ------------------------------------------------------------------------------------

