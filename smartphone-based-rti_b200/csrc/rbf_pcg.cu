@@ -100,12 +100,12 @@ __device__ __forceinline__ float pack_scale(double rmax, double *scale) {
     *scale = scalbn(1.0, 10 - e);
     return (float)scalbn(1.0, e - 10);
 }
-__device__ __forceinline__ void pack_store(uint16_t *packed, long long n_blk, int k_rows, int k_pad, int j, int slot,
-                                           double v) {
+// column `col` of the packed operand: [hi halves of rows 0..k_pad) | lo halves], contiguous (K-major)
+__device__ __forceinline__ void pack_store(uint16_t *packed, long long col, int k_rows, int k_pad, int j, double v) {
     const __half h = __double2half(v);
     const __half l = __double2half(v - (double)__half2float(h));
-    packed[(n_blk * k_rows + j) * PTILE + slot] = __half_as_ushort(h);
-    packed[(n_blk * k_rows + k_pad + j) * PTILE + slot] = __half_as_ushort(l);
+    packed[col * k_rows + j] = __half_as_ushort(h);
+    packed[col * k_rows + k_pad + j] = __half_as_ushort(l);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -442,7 +442,7 @@ rbf_tile_inverse_kernel(const float *__restrict__ lx, const float *__restrict__ 
 //   X, R      float64 [col][r_pad]   iterate and residual
 //   Pv        float32 [col][r_pad]   search direction (rounded once, used rounded)
 //   Z         float64 [col][r_pad]   preconditioned residual of the last contraction, times 1/zscale
-//   packed    fp16 [n_blk][2*k_pad][PTILE], the contraction's vector operand (residual hi rows, lo rows)
+//   packed    fp16 [col][2*k_pad], the contraction's vector operand (residual hi halves, then lo halves)
 //   rz, zscale per column; done, iters per pixel; tile_active per tile.
 // ------------------------------------------------------------------------------------------
 struct PcgState {
@@ -498,8 +498,8 @@ rbf_pcg_init_kernel(const float *__restrict__ lx, const float *__restrict__ ly, 
             st.Pv[col1 * g.r_pad + j] = 0.f;
         }
         if (j < g.k_pad) {
-            pack_store(st.packed, 2 * tb, k_rows, g.k_pad, j, slot, r0[i] * sc0);
-            pack_store(st.packed, 2 * tb + 1, k_rows, g.k_pad, j, slot, r1[i] * sc1);
+            pack_store(st.packed, col0, k_rows, g.k_pad, j, r0[i] * sc0);
+            pack_store(st.packed, col1, k_rows, g.k_pad, j, r1[i] * sc1);
         }
     }
     if (t == 0) {
@@ -639,8 +639,8 @@ rbf_pcg_step_kernel(const float *__restrict__ lx, const float *__restrict__ ly, 
         for (int i = 0; i < ROWS; ++i) {
             const int j = t + i * PCG_THREADS;
             if (j < g.k_pad) {
-                pack_store(st.packed, 2 * tb, k_rows, g.k_pad, j, slot, r0[i] * sc0);
-                pack_store(st.packed, 2 * tb + 1, k_rows, g.k_pad, j, slot, r1[i] * sc1);
+                pack_store(st.packed, col0, k_rows, g.k_pad, j, r0[i] * sc0);
+                pack_store(st.packed, col1, k_rows, g.k_pad, j, r1[i] * sc1);
             }
         }
         if (t == 0) {

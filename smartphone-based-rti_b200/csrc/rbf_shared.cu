@@ -83,6 +83,7 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
 // Instruction descriptor, kind::f16: D fp32 (bit 4), A/B fp16 (format 0), A K-major,
 // B MN-major (bit 16), N >> 3 at [17,23), M >> 4 at [24,29).
 constexpr uint32_t IDESC = (1u << 4) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+constexpr uint32_t IDESC_BK = IDESC & ~(1u << 16);      // B K-major as well (batched form: vectors stored [column][k])
 
 
 // ---- the contraction --------------------------------------------------------------------
@@ -106,7 +107,7 @@ struct GemmArgs {
 
 enum { STORE_TMA = 0, STORE_DIRECT = 1, STORE_F64_PIXEL_MAJOR = 2 };
 
-template <int MODE>
+template <int MODE, bool B_KMAJOR = false>
 __global__ void __launch_bounds__(THREADS, 1)
 rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
                        const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_out,
@@ -168,9 +169,14 @@ rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_
                     mbar_expect_tx(full, STAGE_BYTES);
                     tma_load_2d(sa, &map_hi, a_col, a_row, full);
                     tma_load_2d(sa + A_TILE, &map_lo, a_col, a_row, full);
+                    if (B_KMAJOR) {
+                        // one box of 256 columns x 64 k (each column's k run is contiguous in HBM)
+                        tma_load_2d(sa + 2 * A_TILE, &map_b, kb * BK, n_blk * BN, full);
+                    } else {
 #pragma unroll
-                    for (int j = 0; j < BN / 64; ++j)
-                        tma_load_3d(sa + 2 * A_TILE + j * B_BOX, &map_b, j * 64, kb * BK, n_blk, full);
+                        for (int j = 0; j < BN / 64; ++j)
+                            tma_load_3d(sa + 2 * A_TILE + j * B_BOX, &map_b, j * 64, kb * BK, n_blk, full);
+                    }
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
@@ -197,9 +203,12 @@ rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_
                         const uint64_t da_lo = smem_desc(sa + A_TILE + k * (UK * 2), 16, 1024);
                         // B (MN-major): 64-pixel atoms 8 KB apart (LBO), 8-light groups 1024 B apart (SBO);
                         // a k-step is two 8-light groups
-                        const uint64_t db = smem_desc(sa + 2 * A_TILE + k * (UK * 128), B_BOX, 1024);
-                        tc_mma_f16(d_tmem, da_hi, db, IDESC, (kb | k) != 0);
-                        tc_mma_f16(d_tmem, da_lo, db, IDESC, 1u);
+                        // B K-major (batched form): the same layout as A, 256 rows
+                        const uint64_t db = B_KMAJOR ? smem_desc(sa + 2 * A_TILE + k * (UK * 2), 16, 1024)
+                                                     : smem_desc(sa + 2 * A_TILE + k * (UK * 128), B_BOX, 1024);
+                        constexpr uint32_t idesc = B_KMAJOR ? IDESC_BK : IDESC;
+                        tc_mma_f16(d_tmem, da_hi, db, idesc, (kb | k) != 0);
+                        tc_mma_f16(d_tmem, da_lo, db, idesc, 1u);
                     }
                     tc_commit(bar_empty + 8 * stage);              // smem slot free once these MMAs retire
                     if (kb == num_k - 1) tc_commit(bar_tfull + 8 * acc);
@@ -499,8 +508,8 @@ int gemm_launch(const uint16_t *d_packed, int n, long long n_pixels, const uint1
 
 // Batched contraction for the tile-preconditioned conjugate gradients of rbf_pcg.cu:
 //   out[col][0:op_rows_pad] = (op_hi + op_lo)[col / (blks_per_op*256)] . ([B_hi; B_lo])[:, col]
-// d_packed: fp16 [n_cols/256][k_rows][256] with k_rows = 2 * a_k_pad (hi rows then lo rows of the
-// vector operand); operators: fp16 [n_ops][op_rows_pad][a_k_pad]; out float64 [n_cols][op_rows_pad].
+// d_packed: fp16 [n_cols][k_rows] with k_rows = 2 * a_k_pad (each column: the hi halves then the lo halves
+// of its vector, contiguous -- K-major B operand); operators: fp16 [n_ops][op_rows_pad][a_k_pad]; out float64 [n_cols][op_rows_pad].
 int rbf_gemm_batched(const uint16_t *d_packed, int k_rows, long long n_cols, const uint16_t *d_op_hi,
                      const uint16_t *d_op_lo, const float *d_inv_scale, int n_ops, int op_rows_pad, int a_k_pad,
                      int blks_per_op, double *d_out, const int32_t *d_tile_active, cudaStream_t stream) {
@@ -515,7 +524,9 @@ int rbf_gemm_batched(const uint16_t *d_packed, int k_rows, long long n_cols, con
     if ((rc = make_map_2d(&map_lo, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, d_op_lo, a_k_pad, rows_all, (uint64_t)a_k_pad * 2, BK, BM,
                           "pcg op_lo")))
         return rc;
-    if ((rc = make_map_packed(&map_b, d_packed, k_rows, n_cols / BN))) return rc;
+    if ((rc = make_map_2d(&map_b, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, d_packed, k_rows, n_cols, (uint64_t)k_rows * 2, BK, BN,
+                          "pcg vectors")))
+        return rc;
     GemmArgs args;
     args.op_rows = op_rows_pad;
     args.n = k_rows;
@@ -537,9 +548,10 @@ int rbf_gemm_batched(const uint16_t *d_packed, int k_rows, long long n_cols, con
     const long long tiles = (long long)args.num_m_blks * args.num_n_blks;
     RTI_REQUIRE(tiles < (1ll << 31), "rbf_gemm_batched: too many tiles");
     const int grid = (int)(tiles < sms ? tiles : sms);
-    RTI_CUDA(cudaFuncSetAttribute(rbf_shared_gemm_kernel<STORE_F64_PIXEL_MAJOR>,
+    RTI_CUDA(cudaFuncSetAttribute(rbf_shared_gemm_kernel<STORE_F64_PIXEL_MAJOR, true>,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES));
-    rbf_shared_gemm_kernel<STORE_F64_PIXEL_MAJOR><<<grid, THREADS, SMEM_BYTES, stream>>>(map_hi, map_lo, map_b, map_b, args);
+    rbf_shared_gemm_kernel<STORE_F64_PIXEL_MAJOR, true><<<grid, THREADS, SMEM_BYTES, stream>>>(map_hi, map_lo, map_b, map_b,
+                                                                                                 args);
     RTI_LAUNCHED("rbf_shared_gemm_kernel");
     return RTI_OK;
 }
