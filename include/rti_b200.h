@@ -171,7 +171,8 @@ int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten
  * and scipy's grid values to ~1e-4 of their maximum (north_star allows 1e-3).
  * d_work: rti_rbf_pcg_workspace_bytes(n, tiles) bytes for `tiles` tiles in flight (>= 1; the
  * call batches the slab's tiles through whatever it is given), 256-byte aligned.
- * d_iters: optional int32 [rows*cols], steps each pixel took.  d_bad: int32[2]; [0] counts
+ * d_iters: optional int32 [rows*cols], steps each pixel took (negated for a pixel that did
+ * not converge).  d_bad: int32[2]; [0] counts
  * tiles whose centre matrix is singular (duplicate nodes), [1] pixels that did not reach tol
  * within max_iters steps -- refit those with rti_rbf_fit_soa.  3 <= n <= 1025. */
 int64_t rti_rbf_pcg_workspace_bytes(int n, int64_t tiles);

@@ -31,6 +31,19 @@ from . import constants as _default_constants
 
 _cst = _default_constants           # rebound by install() to the reference's constants module
 
+# Numerical path of the linear-RBF mode (per-pixel lights).  "fast" (default): tile-preconditioned
+# conjugate-gradient fit (rti_rbf_fit_pcg; pixels it cannot converge are refitted by the direct kernel)
+# and float32-distance grid evaluation (rti_rbf_table_fast): grid values within ~2e-4 of the grid
+# maximum of scipy's (north_star allows 1e-3), ~4x faster.  "fp64": direct fp64 Cholesky + fp64
+# evaluation, 1e-8.  The path taken is recorded on InterpolationResult.path.
+RBF_PRECISION = os.environ.get("RTI_RBF_PRECISION", "fast")
+RBF_PCG_MAX_ITERS = 32
+RBF_PCG_TOL = 0.01                  # max-norm node residual, in intensity units
+# Device bytes of one table tile buffer (two are used): prepare_images_data / write_table_file evaluate
+# the [ly][lx] images in ROW TILES of the ROI through these, so the (G, G, P) table never has to fit on
+# the device (42 GB at 1024^2, 671 GB at 4096^2).
+TABLE_TILE_BYTES = 1 << 30
+
 
 def _torch():
     import torch
@@ -168,12 +181,26 @@ class InterpolationResult:
     PTM: coefficient map float64 (6, P);  RBF: nodes (lx, ly) and weights float64 (P, N).
     A pixel's grid is evaluated on demand."""
 
-    def __init__(self, mode, rows, cols, axis, coef=None, lx=None, ly=None, weights=None, row0=0, shared=None):
+    def __init__(self, mode, rows, cols, axis, coef=None, lx=None, ly=None, weights=None, row0=0, shared=None,
+                 stack=None, precision="fp64", path=None):
         self.mode, self.rows, self.cols, self.row0 = mode, rows, cols, row0
         self.axis = np.ascontiguousarray(axis, dtype=np.float64)
-        self.coef, self.lx, self.ly, self.weights = coef, lx, ly, weights
+        self._coef, self.lx, self.ly, self.weights = coef, lx, ly, weights
         self.shared = shared            # mode "rbf_shared": a SharedLightRbf
+        self.stack = stack              # mode "ptm" from frame records: coefficients are fitted on demand, or by
+        self._coef_done = coef is not None   # the fused fit + table kernel while the table is produced
+        self.precision = precision      # "fast" | "fp64" (RBF modes)
+        self.path = path or mode        # which kernels produced / will produce the numbers
         self._d_axis = None
+
+    @property
+    def coef(self):
+        """PTM coefficient map float64 (6, P) on the device (fitted on first use when stack-backed)."""
+        if self.mode == "ptm" and not self._coef_done:
+            coef, bad = _fit_ptm_from_stack(self.stack, out=self._coef)
+            _raise_if_bad(bad, "PTM")
+            self._coef, self._coef_done = coef, True
+        return self._coef
 
     @property
     def n_pixels(self):
@@ -238,9 +265,9 @@ class _ResultRow:
         return self._res.grids(self._y * cols + x % cols, 1)[0]
 
 
-def _fit_ptm_from_stack(stack: FrameStack):
+def _fit_ptm_from_stack(stack: FrameStack, out=None):
     torch = _torch()
-    coef = torch.empty((6, stack.n_pixels), dtype=torch.float64, device="cuda")
+    coef = torch.empty((6, stack.n_pixels), dtype=torch.float64, device="cuda") if out is None else out
     bad = torch.zeros(1, dtype=torch.int32, device="cuda")
     _capi.call("rti_ptm_fit_frames", stack.d_frames.data_ptr(), stack.rows * stack.cols,
                stack.d_cams.data_ptr(), stack.n, stack.row0, stack.rows, stack.cols,
@@ -445,10 +472,14 @@ def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
              and data[0]._soa is data[1]._soa is data[2]._soa
              and data[0].shape[:2] == (range_val, range_val))
     if fused:
+        # straight from the uint8 frame records: nothing runs yet.  prepare_images_data / write_table_file fit
+        # and evaluate row tile by row tile with the fused kernel (rti_ptm_fit_table_frames); touching
+        # res[y][x] or res.coefficients() first fits with rti_ptm_fit_frames instead.
         stack = data[0]._soa.stack
-        coef, bad = _fit_ptm_from_stack(stack)
-        _raise_if_bad(bad, "PTM")
-        return InterpolationResult("ptm", range_val, range_val, axis, coef=coef, row0=stack.row0)
+        if stack.n < 6:
+            raise ValueError("PTM needs >= 6 light samples, got %d (analysis.py:296-298 fails in np.dot)" % stack.n)
+        return InterpolationResult("ptm", range_val, range_val, axis, row0=stack.row0, stack=stack,
+                                   path="ptm: fused gather+fit+table per row tile (rti_ptm_fit_table_frames)")
 
     lx, ly, inten = _as_device_soa(data, range_val)
     n_pixels, n = lx.shape
@@ -466,16 +497,23 @@ def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
         if res.shared.pack_soa(inten):     # intensities exact in fp16 (always true for uint8 frames)
             res.shared.operator(0)
             return res
-    weights = rbf_fit_device(lx, ly, inten, bad)
+    precision = RBF_PRECISION if RBF_PRECISION in ("fast", "fp64") else "fast"
+    if precision == "fast" and 3 <= n <= 1025:
+        weights, info = rbf_fit_device_pcg(lx, ly, inten, range_val, range_val, bad)
+        path = "rbf: pcg fit (%d of %d pixels refitted directly) + float32-distance table" % (info["refit"], n_pixels)
+    else:
+        weights = rbf_fit_device(lx, ly, inten, bad)
+        path = "rbf: direct fp64 fit + %s table" % ("float32-distance" if precision == "fast" else "fp64")
     _raise_if_bad(bad, "RBF")
-    return InterpolationResult("rbf", range_val, range_val, axis, lx=lx, ly=ly, weights=weights)
+    return InterpolationResult("rbf", range_val, range_val, axis, lx=lx, ly=ly, weights=weights,
+                               precision=precision, path=path)
 
 
-def rbf_fit_device(lx, ly, inten, bad):
-    """Linear-RBF weights (P, N) float64 for device SoA tensors (scipy Rbf.__init__)."""
+def rbf_fit_device(lx, ly, inten, bad, out=None):
+    """Linear-RBF weights (P, N) float64 for device SoA tensors (scipy Rbf.__init__), direct fp64 solve."""
     torch = _torch()
     n_pixels, n = lx.shape
-    weights = torch.empty((n_pixels, n), dtype=torch.float64, device="cuda")
+    weights = torch.empty((n_pixels, n), dtype=torch.float64, device="cuda") if out is None else out
     free, _total = torch.cuda.mem_get_info()
     lib = _capi.load()
     per_pixel = max(1, lib.rti_rbf_workspace_bytes(n, 1))
@@ -487,6 +525,47 @@ def rbf_fit_device(lx, ly, inten, bad):
     return weights
 
 
+def rbf_fit_device_pcg(lx, ly, inten, rows, cols, bad, max_iters=None, tol=None):
+    """Linear-RBF weights of a rows x cols slab by the tile-preconditioned conjugate gradients
+    (rti_rbf_fit_pcg); pixels that did not converge (neighbouring pixels' nodes too different from the tile
+    centre's: data that does not come from compute_intensities) and the pixels of tiles whose centre is
+    singular are refitted with the direct fp64 kernel, which also reports genuinely singular pixels in `bad`.
+    Returns (weights, info)."""
+    torch = _torch()
+    lib = _capi.load()
+    n_pixels, n = lx.shape
+    assert n_pixels == rows * cols
+    max_iters = RBF_PCG_MAX_ITERS if max_iters is None else max_iters
+    tol = RBF_PCG_TOL if tol is None else tol
+    weights = torch.empty((n_pixels, n), dtype=torch.float64, device="cuda")
+    tiles = ((rows + 15) // 16) * ((cols + 15) // 16)
+    free, _total = torch.cuda.mem_get_info()
+    per_tile = lib.rti_rbf_pcg_workspace_bytes(n, 2) - lib.rti_rbf_pcg_workspace_bytes(n, 1)
+    in_flight = int(max(1, min(tiles, (free // 2) // max(per_tile, 1), 4096)))
+    work_bytes = lib.rti_rbf_pcg_workspace_bytes(n, in_flight)
+    work = torch.empty(work_bytes, dtype=torch.uint8, device="cuda")
+    iters = torch.empty(n_pixels, dtype=torch.int32, device="cuda")
+    pbad = torch.zeros(2, dtype=torch.int32, device="cuda")
+    _capi.call("rti_rbf_fit_pcg", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), rows, cols, n, weights.data_ptr(),
+               work.data_ptr(), work_bytes, max_iters, float(tol), iters.data_ptr(), pbad.data_ptr(),
+               _stream_ptr(torch))
+    del work
+    singular_tiles, unconverged = (int(v) for v in pbad.tolist())
+    info = {"singular_tiles": singular_tiles, "refit": 0, "max_iters": max_iters, "tol": tol}
+    if singular_tiles or unconverged:
+        redo = iters <= 0 if singular_tiles == 0 else (iters <= 0) | ~torch.isfinite(weights).all(dim=1)
+        if singular_tiles:
+            # a singular tile centre leaves its whole tile without a preconditioner
+            redo |= iters >= max_iters
+        idx = redo.nonzero().view(-1)
+        info["refit"] = int(idx.numel())
+        if idx.numel():
+            w_sub = rbf_fit_device(lx[idx].contiguous(), ly[idx].contiguous(), inten[idx].contiguous(), bad)
+            weights[idx] = w_sub
+    info["steps_mean"] = float(iters.abs().float().mean().item())
+    return weights, info
+
+
 def _raise_if_bad(bad, what):
     count = int(bad.item())          # synchronises: numerical failures surface here
     if count > 0:
@@ -495,27 +574,94 @@ def _raise_if_bad(bad, what):
 
 
 # ----------------------------------------------------------------------------- table
+def _table_rows(res: InterpolationResult, r0, tr, out, bad):
+    """Rows [r0, r0 + tr) of every [ly][lx] image into out, an int32 (G*G, tr*cols) device tensor
+    (bad: int32[2] device counters: [0] singular PTM pixels, [1] values that do not fit int32)."""
+    torch = _torch()
+    g = res.axis.size
+    cols = res.cols
+    p0, tp = r0 * cols, tr * cols
+    S = _stream_ptr(torch)
+    if res.mode == "ptm" and not res._coef_done and res.stack is not None:
+        st = res.stack
+        if res._coef is None:
+            res._coef = torch.empty((6, st.n_pixels), dtype=torch.float64, device="cuda")
+        # fused gather + fit + table of this row tile; the coefficient map fills in as a by-product
+        _capi.call("rti_ptm_fit_table_frames", st.d_frames.data_ptr() + p0, st.n_pixels, st.d_cams.data_ptr(), st.n,
+                   st.row0 + r0, tr, cols, res.d_axis().data_ptr(), g, res._coef.data_ptr() + 8 * p0, st.n_pixels,
+                   out.data_ptr(), tp, bad.data_ptr(), S)
+        if r0 + tr >= res.rows:
+            res._coef_done = True          # (a caller that stops early refits on demand)
+    elif res.mode == "ptm":
+        _capi.call("rti_ptm_table", res.coef.data_ptr() + 8 * p0, res.n_pixels, tp, res.d_axis().data_ptr(), g,
+                   out.data_ptr(), tp, bad.data_ptr() + 4, S)
+    elif res.mode == "rbf_shared":
+        if (r0, tr) != (0, res.rows):
+            raise ValueError("shared-light tables are produced in one piece")
+        res.shared.table(out, tp, bad[1:])
+    else:
+        n = res.weights.shape[1]
+        fn = "rti_rbf_table_fast" if res.precision == "fast" else "rti_rbf_table"
+        _capi.call(fn, res.lx.data_ptr() + 4 * p0 * n, res.ly.data_ptr() + 4 * p0 * n,
+                   res.weights.data_ptr() + 8 * p0 * n, tp, n, res.d_axis().data_ptr(), g, out.data_ptr(), tp,
+                   bad.data_ptr() + 4, S)
+
+
+def _raise_if_bad_table(bad):
+    singular, unrepresentable = (int(v) for v in bad.tolist())       # synchronises
+    if singular > 0:
+        raise _capi.RtiSingularError(_capi.RTI_ERR_SINGULAR, "PTM: %d pixel(s) have a singular system" % singular)
+    if unrepresentable > 0:
+        # analysis.py:407 raises ValueError (NaN/inf) or OverflowError (out of int32 range)
+        raise ValueError("cannot convert interpolated values to int32 (NaN, inf or out of range)")
+
+
 def table_device(res: InterpolationResult, out=None):
-    """int32 (G, G, P) table of a result on the device (prepare_images_data layout)."""
+    """int32 (G, G, P) table of a result on the device (prepare_images_data layout) -- the WHOLE table;
+    prepare_images_data and write_table_file go through table_tiles() instead."""
     torch = _torch()
     g = res.axis.size
     p = res.n_pixels
     if out is None:
         out = torch.empty((g, g, p), dtype=torch.int32, device="cuda")
-    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
-    if res.mode == "ptm":
-        _capi.call("rti_ptm_table", res.coef.data_ptr(), p, p, res.d_axis().data_ptr(), g,
-                   out.data_ptr(), p, bad.data_ptr(), _stream_ptr(torch))
-    elif res.mode == "rbf_shared":
-        res.shared.table(out, p, bad)
-    else:
-        n = res.weights.shape[1]
-        _capi.call("rti_rbf_table", res.lx.data_ptr(), res.ly.data_ptr(), res.weights.data_ptr(), p, n,
-                   res.d_axis().data_ptr(), g, out.data_ptr(), p, bad.data_ptr(), _stream_ptr(torch))
-    if int(bad.item()) > 0:
-        # analysis.py:407 raises ValueError (NaN/inf) or OverflowError (out of int32 range)
-        raise ValueError("cannot convert interpolated values to int32 (NaN, inf or out of range)")
+    bad = torch.zeros(2, dtype=torch.int32, device="cuda")
+    _table_rows(res, 0, res.rows, out.view(g * g, p), bad)
+    _raise_if_bad_table(bad)
     return out
+
+
+def table_tiles(res: InterpolationResult, tile_bytes=None):
+    """Yields (r0, tr, d_tile): rows [r0, r0 + tr) of every image as an int32 (G*G, tr*cols) device
+    tensor, produced through two alternating device buffers of at most tile_bytes each; tile t + 1 is
+    being computed while the caller consumes tile t.  Numerical failures raise after the last tile."""
+    torch = _torch()
+    g = res.axis.size
+    gg = g * g
+    tile_bytes = TABLE_TILE_BYTES if tile_bytes is None else tile_bytes
+    tr_max = int(max(1, min(res.rows, tile_bytes // max(1, gg * 4 * res.cols))))
+    if res.mode == "rbf_shared":
+        tr_max = res.rows
+    # whole 16-byte granules per tile keep the fused kernel's frame rows aligned (its fast path)
+    while tr_max < res.rows and (tr_max * res.cols) % 16 != 0:
+        tr_max += 1
+    tiles = [(r0, min(tr_max, res.rows - r0)) for r0 in range(0, res.rows, tr_max)]
+    nbuf = 1 if len(tiles) == 1 else 2
+    bufs = [torch.empty(gg * tr_max * res.cols, dtype=torch.int32, device="cuda") for _ in range(nbuf)]
+    bad = torch.zeros(2, dtype=torch.int32, device="cuda")
+
+    def issue(t):
+        r0, tr = tiles[t]
+        view = bufs[t % nbuf][:gg * tr * res.cols].view(gg, tr * res.cols)
+        _table_rows(res, r0, tr, view, bad)
+        return view
+
+    nxt = issue(0)
+    for t, (r0, tr) in enumerate(tiles):
+        cur = nxt
+        if t + 1 < len(tiles):
+            nxt = issue(t + 1)             # its buffer was consumed (synchronously) two tiles ago
+        yield r0, tr, cur
+    _raise_if_bad_table(bad)
 
 
 _PINNED = {}          # (device, bytes) -> two pinned staging tensors, reused across calls
@@ -574,6 +720,26 @@ def _table_to_host(d_table):
     return out
 
 
+def _table_to_host_tiled(res):
+    """The whole (G*G, P) table as a fresh host ndarray, evaluated in row tiles on the device."""
+    from concurrent.futures import ThreadPoolExecutor
+    gg = res.axis.size ** 2
+    out = np.empty((gg, res.rows, res.cols), dtype=np.int32)
+    threads = max(1, min(8, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else 4))
+    with ThreadPoolExecutor(threads) as pool:
+        for r0, tr, d_tile in table_tiles(res):
+            def consume(chunk, i0, r0=r0, tr=tr):
+                cnt = chunk.shape[0]
+                step = (cnt + threads - 1) // threads
+                src = chunk.reshape(cnt, tr, res.cols)
+                futs = [pool.submit(np.copyto, out[i0 + a:i0 + min(cnt, a + step), r0:r0 + tr],
+                                    src[a:min(cnt, a + step)]) for a in range(0, cnt, step)]
+                for f in futs:
+                    f.result()
+            _stream_images(d_tile, consume)
+    return out.reshape(gg, res.rows * res.cols)
+
+
 def prepare_images_data(data, first_only=False):
     """Prepare images for each light position (analysis.py:375-411).
 
@@ -590,7 +756,7 @@ def prepare_images_data(data, first_only=False):
         if (data.rows, data.cols) != (range_val, range_val):
             raise IndexError("interpolation result is %dx%d, ROI is %d" % (data.rows, data.cols, range_val))
         g = data.axis.size
-        table = _table_to_host(table_device(data).view(g * g, -1)).reshape(g, g, range_val, range_val)
+        table = _table_to_host_tiled(data).reshape(g, g, range_val, range_val)
     else:
         # plain nested list / array [y][x][ly][lx]: transpose + truncate on the device
         grids = np.ascontiguousarray(
@@ -701,13 +867,28 @@ def write_table_file(res, filename):
         raise IndexError("interpolation result is %dx%d, ROI is %d" % (res.rows, res.cols, _cst.ROI_DIAMETER))
     print("Preparing images values:")
     g = res.axis.size
-    d_table = table_device(res).view(g * g, -1)
+    if not table_io.template_ok((res.rows, res.cols), np.int32):
+        # this numpy pickles ndarrays in a way the streaming writers do not know: plain pickle.dump
+        return write_on_file(prepare_images_data(res), filename, compressed=False)
     print("Writing on file {}".format(filename))
     filename = filename + ".pickle"
-    with open(filename, "wb") as f:
-        writer = table_io.TableStreamWriter(g, g, (res.rows, res.cols), np.int32, f)
-        # the D2H copy of the next chunk runs while this chunk is written
-        _stream_images(d_table, lambda chunk, i0: writer.write_images(chunk.reshape(-1, res.rows, res.cols)))
+    from concurrent.futures import ThreadPoolExecutor
+    writer = table_io.TableTileWriter(g, g, (res.rows, res.cols), np.int32, filename)
+    threads = max(1, min(8, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else 4))
+    try:
+        with ThreadPoolExecutor(threads) as pool:
+            # row tiles of the ROI: device tile -> pinned ring -> pwrite at each image's fixed offset; the
+            # D2H copy of the next chunk and the evaluation of the next tile run while this chunk is written
+            for r0, tr, d_tile in table_tiles(res):
+                def consume(chunk, i0, r0=r0):
+                    cnt = chunk.shape[0]
+                    step = (cnt + threads - 1) // threads
+                    futs = [pool.submit(writer.write_rows, i0 + a, chunk[a:min(cnt, a + step)], r0)
+                            for a in range(0, cnt, step)]
+                    for f in futs:
+                        f.result()
+                _stream_images(d_tile, consume)
+    finally:
         writer.close()
     print("Saved file {}".format(filename))
 

@@ -701,8 +701,9 @@ rbf_pcg_finish_kernel(const float *__restrict__ lx, const float *__restrict__ ly
     block_reduce<1, false>(sw, s_red);
     if (t == 0) {
         weights[pix * n] = sigma - sw[0];
-        if (iters_out != nullptr) iters_out[pix] = st.iters[pidx];
-        if (st.done[pidx] == 0 && bad != nullptr) atomicAdd(bad + 1, 1);      // not converged within max_iters
+        const bool unconverged = st.done[pidx] == 0;                          // not below tol within max_iters
+        if (iters_out != nullptr) iters_out[pix] = unconverged ? -st.iters[pidx] : st.iters[pidx];
+        if (unconverged && bad != nullptr) atomicAdd(bad + 1, 1);
     }
 }
 

@@ -721,24 +721,88 @@ def test_rbf_duplicate_nodes_are_flagged(torch_cuda):
     # ~1e16-sized weights depending on the host, so the oracle is not asserted on here)
 
 
-def test_rbf_call_surface(torch_cuda, ref_small, monkeypatch):
+@pytest.mark.parametrize("precision", ["fp64", "fast"])
+def test_rbf_call_surface(torch_cuda, ref_small, monkeypatch, precision):
+    """interpolate_intensities(data) + prepare_images_data in linear-RBF mode against the reference's own
+    outputs, on both numerical paths: "fp64" (direct Cholesky, fp64 evaluation) and the default "fast"
+    (tile-preconditioned CG with direct refits + float32-distance table; north_star: 1e-3)."""
     import rti_b200
-    from rti_b200 import synthetic
+    from rti_b200 import analysis, synthetic
     frames, cams = ref_small["frames"], ref_small["cams"]
     monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", frames.shape[1])
+    monkeypatch.setattr(analysis, "RBF_PRECISION", precision)
     data = rti_b200.compute_intensities(synthetic.as_records(frames, cams))
     res = rti_b200.interpolate_intensities(data)                       # interpolate_PTM=False: RBF
+    assert res.precision == precision and res.path.startswith("rbf:")
+    rtol = RBF_GRID_RTOL if precision == "fp64" else 2e-4
     for k, (y, x) in enumerate(ref_small["keep"]):
         r = ref_small["rbf_grids"][k]
-        assert np.max(np.abs(res[y][x] - r)) <= RBF_GRID_RTOL * np.max(np.abs(r))
+        assert np.max(np.abs(res[y][x] - r)) <= rtol * np.max(np.abs(r))
     table = np.array(rti_b200.prepare_images_data(res))
     diff = table != ref_small["table_rbf"]
-    assert np.count_nonzero(diff) <= 1e-5 * diff.size + 1
+    if precision == "fp64":
+        assert np.count_nonzero(diff) <= 1e-5 * diff.size + 1
+    else:
+        # entries may flip by one where the fp64 value is within the path's tolerance of an integer
+        grids = orc.interpolate(ref_small["lx"], ref_small["ly"], ref_small["inten"], ptm=False)
+        gt = np.transpose(grids, (2, 3, 0, 1))
+        assert np.all(np.abs(table - ref_small["table_rbf"]) <= 1)
+        assert np.all(np.abs(gt[diff] - np.rint(gt[diff])) <= RBF_FAST_RTOL * np.max(np.abs(gt)))
     # singular pixels surface as an ArithmeticError subclass
     lx, ly, inten = (np.array(ref_small[k]) for k in ("lx", "ly", "inten"))
     lx[0, 0, 5], ly[0, 0, 5] = lx[0, 0, 6], ly[0, 0, 6]
     with pytest.raises(rti_b200.RtiSingularError):
         rti_b200.interpolate_intensities((lx, ly, inten))
+
+
+@pytest.mark.parametrize("ptm", [True, False])
+def test_compute_tiles_table_under_device_memory_cap(torch_cuda, monkeypatch, tmp_path, ptm):
+    """compute() evaluates the table in row tiles through a bounded device buffer and
+    pwrites them into the reference's pickle layout, so a table larger than the device memory it is allowed
+    still comes out right.  ROI 96 x 96 (368 MB table) under a 256 MB torch allocator cap with 24 MB tiles;
+    sampled pixels against the oracle, every image against the untiled device table."""
+    import pickle
+    import rti_b200
+    from rti_b200 import analysis, synthetic
+    torch = torch_cuda
+    r, n = 96, 12 if ptm else 24
+    frames, cams = synthetic.lambertian_stack(r, r, n, seed=21, rows_total=1024, row0=300)
+    path = str(tmp_path / "frames_results_cap")
+    rti_b200.write_on_file(synthetic.as_records(frames, cams), path)
+    monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", r)
+    monkeypatch.setattr(analysis, "TABLE_TILE_BYTES", 24 << 20)
+    monkeypatch.chdir(tmp_path)
+    (tmp_path / "assets").mkdir()
+    total = torch.cuda.get_device_properties(0).total_memory
+    torch.cuda.empty_cache()
+    torch.cuda.set_per_process_memory_fraction(min(1.0, (256 << 20) / total))
+    try:
+        rti_b200.compute("cap", from_storage=True, storage_filepath=path, interpolate_PTM=ptm)
+    finally:
+        torch.cuda.set_per_process_memory_fraction(1.0)
+    with open(tmp_path / "assets" / "interpolation_results_cap.pickle", "rb") as f:
+        images = pickle.load(f)
+    assert len(images) == 100 and len(images[0]) == 100 and images[99][99].shape == (r, r)
+    assert images[3][7].dtype == np.int32 and images[3][7].flags.writeable
+    table = np.array(images)                                          # (100, 100, r, r)
+    lx, ly, inten = orc.gather_soa(frames, cams)                      # compute() numbers the ROI rows from 0
+    ax = orc.light_axis()
+    rng = np.random.default_rng(2)
+    for _ in range(10):
+        y, x = int(rng.integers(r)), int(rng.integers(r))
+        if ptm:
+            ref = orc.ptm_grid(orc.ptm_fit(lx[y, x], ly[y, x], inten[y, x]), ax)
+            assert np.array_equal(table[:, :, y, x], np.trunc(ref).astype(np.int32))
+        else:
+            ref = orc.rbf_grid(lx[y, x], ly[y, x], orc.rbf_fit(lx[y, x], ly[y, x], inten[y, x]), ax)
+            d = table[:, :, y, x] != np.trunc(ref).astype(np.int32)
+            assert np.all(np.abs(table[:, :, y, x] - np.trunc(ref)) <= 1)
+            assert np.all(np.abs(ref[d] - np.rint(ref[d])) <= RBF_FAST_RTOL * np.max(np.abs(ref)))
+    # and the tiled file equals the table evaluated in one piece
+    data = rti_b200.compute_intensities(synthetic.as_records(frames, cams))
+    res = rti_b200.interpolate_intensities(data, interpolate_PTM=ptm)
+    whole = analysis.table_device(res).view(100, 100, r, r).cpu().numpy()
+    assert np.array_equal(whole, table)
 
 
 # ------------------------------------------------------------------------- fused kernel

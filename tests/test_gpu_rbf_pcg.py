@@ -93,4 +93,4 @@ def test_pcg_reports_unconverged_pixels(torch_cuda):
     lx, ly, inten = slab(16, 16, 130, seed=9)
     _, iters, bad = fit_pcg(torch_cuda, lx, ly, inten, max_iters=2)
     assert bad[0] == 0 and bad[1] > 0
-    assert bad[1] == np.count_nonzero(iters == 2) - 0 or bad[1] <= 256
+    assert bad[1] == np.count_nonzero(iters < 0) and np.all(np.abs(iters) <= 2)
