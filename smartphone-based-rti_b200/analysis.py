@@ -674,11 +674,12 @@ def _stream_images(d_table, consume, chunk_bytes=128 << 20):
     torch = _torch()
     n_images, p = d_table.shape
     per = max(1, min(n_images, chunk_bytes // max(1, p * 4)))
-    key = (d_table.device.index, per * p)
-    if key not in _PINNED:
-        _PINNED.clear()
-        _PINNED[key] = [torch.empty((per, p), dtype=torch.int32, pin_memory=True) for _ in range(2)]
-    bufs = _PINNED[key]
+    elems = max(per * p, chunk_bytes // 4)
+    key = d_table.device.index
+    if key not in _PINNED or _PINNED[key][0].numel() < per * p:
+        _PINNED.pop(key, None)
+        _PINNED[key] = [torch.empty(elems, dtype=torch.int32, pin_memory=True) for _ in range(2)]
+    bufs = [b[:per * p].view(per, p) for b in _PINNED[key]]
     side = torch.cuda.Stream()
     side.wait_stream(torch.cuda.current_stream())
     events = [torch.cuda.Event(), torch.cuda.Event()]

@@ -64,6 +64,9 @@ def main():
     ap.add_argument("--json", default=None)
     ap.add_argument("--dir", default=None, help="working directory (default: a temporary one)")
     ap.add_argument("--skip-rbf", action="store_true")
+    ap.add_argument("--big", action="store_true",
+                    help="large ROI (e.g. 1024 x 500 lights: 42 GB result): skip the whole-table reloads and the "
+                         "separate-calls route, check sampled images through the mmap loader only")
     args = ap.parse_args()
     torch.cuda.set_device(0)
     r, n = args.roi, args.lights
@@ -73,6 +76,11 @@ def main():
     os.chdir(work)
     out = {"config": "synthetic frames_results_synth.pbz2, ROI %d x %d, %d light samples, 100x100 light grid" % (r, r, n),
            "units_pixel_lights": r * r * n}
+    need = r * r * 10000 * 4 * 1.05
+    free = shutil.disk_usage(work).free
+    if free < need:
+        print(json.dumps({"skipped": "result file needs %.1f GB, %.1f GB free under %s" % (need / 1e9, free / 1e9, work)}))
+        return
     try:
         t0 = time.perf_counter()
         frames, cams = synthetic.lambertian_stack(r, r, n, seed=0)
@@ -97,6 +105,24 @@ def main():
                     setattr(analysis, k, fn)
             path = "assets/interpolation_results_synth.pickle"
             size = os.path.getsize(path)
+            if args.big:
+                t0 = time.perf_counter()
+                mapped = analysis.read_from_file("assets/interpolation_results_synth", compressed=False)
+                map_s = time.perf_counter() - t0
+                data = analysis.compute_intensities(analysis.read_from_file("assets/frames_results_synth"))
+                res = analysis.interpolate_intensities(data, interpolate_PTM=ptm)
+                ok = len(mapped) == 100 and len(mapped[0]) == 100 and mapped[3][7].shape == (r, r)
+                for y in (0, r // 2, r - 1):                        # three ROI rows of four images, re-evaluated
+                    gr = res.grids(y * r, r)                        # (r, 100, 100) fp64
+                    for v, u in ((0, 0), (3, 7), (50, 50), (99, 99)):
+                        ok = ok and bool(np.array_equal(mapped[v][u][y], np.trunc(gr[:, v, u]).astype(np.int32)))
+                out[mode] = {"total_s": total, "stages_s": st.times, "result_bytes": size, "mapped_load_s": map_s,
+                             "result_file_ok": bool(ok), "path": res.path,
+                             "mpixel_lights_per_s_wall": r * r * n / total / 1e6}
+                print(mode, json.dumps(out[mode]), flush=True)
+                del mapped
+                os.remove(path)
+                continue
             t0 = time.perf_counter()
             with open(path, "rb") as f:
                 back = pickle.load(f)
