@@ -234,29 +234,87 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
         return min(out)
 
     res = {}
-    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
-    # ---- per-pixel lights: rows [0, 2) of the slab
-    px = 2 * COLS
+    bad = torch.zeros(2, dtype=torch.int32, device="cuda")
+    sm_peak = 148 * 16 * 1.965e9                 # square roots per second: 16 per clock per SM
+    # ---- per-pixel lights (the reference's semantics), default "fast" path: rows [0, 32) of the slab
+    rows_s = 32
+    px = rows_s * COLS
     lx = torch.empty((px, N_LIGHTS), dtype=torch.float32, device="cuda")
     ly = torch.empty_like(lx)
     inten = torch.empty((px, N_LIGHTS), dtype=torch.int32, device="cuda")
-    _capi.call("rti_gather_soa", d_frames.data_ptr(), p, d_cams.data_ptr(), N_LIGHTS, 0, 2, COLS,
+    _capi.call("rti_gather_soa", d_frames.data_ptr(), p, d_cams.data_ptr(), N_LIGHTS, 0, rows_s, COLS,
                lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), S)
     w = torch.empty((px, N_LIGHTS), dtype=torch.float64, device="cuda")
+    tiles = (rows_s // 16) * (COLS // 16)
+    nbytes = lib.rti_rbf_pcg_workspace_bytes(N_LIGHTS, tiles)
+    work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    iters = torch.empty(px, dtype=torch.int32, device="cuda")
+    tab = torch.empty((G, G, px), dtype=torch.int32, device="cuda")
+    max_iters, tol = 32, 0.01
+
+    def pcg():
+        bad.zero_()
+        _capi.call("rti_rbf_fit_pcg", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), rows_s, COLS, N_LIGHTS,
+                   w.data_ptr(), work.data_ptr(), nbytes, max_iters, tol, iters.data_ptr(), bad.data_ptr(), S)
+
+    fit_ms = best(pcg)
+    singular_tiles, unconverged = (int(v) for v in bad.tolist())
+    bad.zero_()
+    ev_ms = best(lambda: _capi.call("rti_rbf_table_fast", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), px, N_LIGHTS,
+                                    d_axis.data_ptr(), G, tab.data_ptr(), px, bad.data_ptr(), S))
+    steps = iters.abs().float()
+    # sampled oracle check (scipy's algorithm in fp64: solve(A, d), cdist(grid, nodes) @ w)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import rti_oracle as orc
+    ax = orc.light_axis()
+    rng = np.random.default_rng(5)
+    worst, flips = 0.0, 0
+    sample_px = rng.integers(0, px, 8)
+    for q in sample_px:
+        q = int(q)
+        l1, l2, dd = lx[q].cpu().numpy(), ly[q].cpu().numpy(), inten[q].cpu().numpy()
+        ref = orc.rbf_grid(l1, l2, orc.rbf_fit(l1, l2, dd), ax)
+        got = orc.rbf_grid(l1, l2, w[q].cpu().numpy(), ax)
+        worst = max(worst, float(np.max(np.abs(got - ref)) / np.max(np.abs(ref))))
+        t = tab[:, :, q].cpu().numpy()
+        d = t != np.trunc(ref).astype(np.int32)
+        flips += int(np.count_nonzero(d & (np.abs(ref - np.rint(ref)) > 1e-3 * np.max(np.abs(ref)))))
+    res["rbf_per_pixel_lights"] = {
+        "sample": "%d pixels (%d ROI rows) x %d lights, fit + 100x100 table" % (px, rows_s, N_LIGHTS),
+        "path": "tile-preconditioned CG fit (rti_rbf_fit_pcg: fp64 DMMA tile inverse, float32 distances + fp64 sums, "
+                "batched tcgen05 preconditioner) + float32-distance table (rti_rbf_table_fast)",
+        "fit_ms": fit_ms, "table_ms": ev_ms, "value": px * N_LIGHTS / ((fit_ms + ev_ms) * 1e-3) / 1e6, "unit": UNIT,
+        "fit_us_per_pixel": fit_ms * 1e3 / px, "table_us_per_pixel": ev_ms * 1e3 / px,
+        "cg_steps": {"mean": float(steps.mean().item()), "max": int(steps.max().item()), "limit": max_iters,
+                     "tol": tol, "unconverged": unconverged},
+        "roofline": {"bound": "sfu", "kernel": "rbf_eval_f32_kernel",
+                     "achieved": G * G * N_LIGHTS * px / (ev_ms * 1e-3) / 1e12, "peak": sm_peak / 1e12,
+                     "unit": "Tsqrt/s", "frac": G * G * N_LIGHTS * px / (ev_ms * 1e-3) / sm_peak,
+                     "note": "G*G*N square roots per pixel on MUFU; peak = 148 SM x 16 per clock x 1.965 GHz "
+                             "(nominal SFU rate; MEASURED_PEAKS.json has no SFU figure)"},
+        "parity_sample": {"pixels": int(len(sample_px)), "grid_max_rel": worst, "tolerance": 1e-3,
+                          "table_entries_off_beyond_tolerance": flips},
+        "singular_tiles": singular_tiles, "unrepresentable": int(bad[0].item())}
+    del work, tab, iters
+    # ---- the same on the fp64 path (direct DMMA Cholesky + fp64 evaluation), rows [0, 2)
+    px2 = 2 * COLS
     batch = 148 * 2
     nbytes = lib.rti_rbf_workspace_bytes(N_LIGHTS, batch)
     work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-    tab = torch.empty((G, G, px), dtype=torch.int32, device="cuda")
-    fit_ms = best(lambda: _capi.call("rti_rbf_fit_soa", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), px, N_LIGHTS,
-                                     w.data_ptr(), work.data_ptr(), nbytes, batch, bad.data_ptr(), S))
-    ev_ms = best(lambda: _capi.call("rti_rbf_table", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), px, N_LIGHTS,
-                                    d_axis.data_ptr(), G, tab.data_ptr(), px, bad.data_ptr(), S))
-    res["rbf_per_pixel_lights"] = {
-        "sample": "%d pixels (2 ROI rows) x %d lights, fit + 100x100 table" % (px, N_LIGHTS),
-        "fit_ms": fit_ms, "table_ms": ev_ms, "value": px * N_LIGHTS / ((fit_ms + ev_ms) * 1e-3) / 1e6, "unit": UNIT,
-        "fit_fp64_tflops": (N_LIGHTS ** 3 / 3.0) * 2 * px / (fit_ms * 1e-3) / 1e12,
-        "bound": "fp64 tensor pipe (fit), fp64 pipe (evaluation)", "singular": int(bad.item())}
+    tab = torch.empty((G, G, px2), dtype=torch.int32, device="cuda")
+    bad.zero_()
+    fit2 = best(lambda: _capi.call("rti_rbf_fit_soa", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), px2, N_LIGHTS,
+                                   w.data_ptr(), work.data_ptr(), nbytes, batch, bad.data_ptr(), S))
+    ev2 = best(lambda: _capi.call("rti_rbf_table", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), px2, N_LIGHTS,
+                                  d_axis.data_ptr(), G, tab.data_ptr(), px2, bad.data_ptr() + 4, S))
+    res["rbf_per_pixel_lights"]["fp64_path"] = {
+        "sample": "%d pixels (2 ROI rows)" % px2, "fit_ms": fit2, "table_ms": ev2,
+        "value": px2 * N_LIGHTS / ((fit2 + ev2) * 1e-3) / 1e6, "unit": UNIT,
+        "fit_fp64_tflops": (N_LIGHTS ** 3 / 3.0) * 2 * px2 / (fit2 * 1e-3) / 1e12,
+        "bound": "fp64 tensor pipe (fit; 37 TFLOP/s DMMA peak is this repo's own microbenchmark, "
+                 "tools/peak_fp64.cu), fp64 pipe (evaluation)"}
     del lx, ly, inten, w, work, tab
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
     # ---- shared lights: rows [0, 256) of the slab, nodes = the light vectors seen from the ROI centre
     rows = 256
     px = rows * COLS
