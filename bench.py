@@ -462,6 +462,92 @@ def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
     P = R4 * R4
     alg = (N4 + 48 + 4 * G * G) * P
     gather_bytes = 48 * (P - P_loc) if world > 1 else 0
+
+    def max_over_ranks(vals):
+        tt = torch.tensor(vals, dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return [float(v) for v in tt.tolist()]
+
+    def timed(fn):
+        fn()
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        barrier()
+        return a.elapsed_time(b)
+
+    # ---- linear RBF at the same split.  (1) shared lights (nodes = light vectors seen from the ROI centre):
+    # operator per rank, then pack + tcgen05 contraction of every sub-slab of the rank's rows (complete run)
+    c = np.array([R4 / 2.0, R4 / 2.0, 0.0])
+    lv = (cams - c) / np.linalg.norm(cams - c, axis=1, keepdims=True)
+    d_lx1 = torch.from_numpy(lv[:, 0].astype(np.float32)).cuda()
+    d_ly1 = torch.from_numpy(lv[:, 1].astype(np.float32)).cuda()
+    op_rows = G * G
+    elems = lib.rti_rbf_shared_operator_elems(op_rows, N4)
+    hi = torch.empty(elems, dtype=torch.int16, device="cuda")
+    lo = torch.empty(elems, dtype=torch.int16, device="cuda")
+    inv = torch.empty(op_rows, dtype=torch.float32, device="cuda")
+    packed = torch.empty(lib.rti_rbf_shared_packed_elems(N4, sub_px), dtype=torch.int16, device="cuda")
+    sbad = torch.zeros(2, dtype=torch.int32, device="cuda")
+    op_ms = timed(lambda: _capi.call("rti_rbf_shared_operator", d_lx1.data_ptr(), d_ly1.data_ptr(), N4, d_axis.data_ptr(),
+                                     G, 0, hi.data_ptr(), lo.data_ptr(), inv.data_ptr(), sbad.data_ptr(), S))
+
+    def run_shared():
+        for y in range(0, nr, SUB):
+            rr = min(SUB, nr - y)
+            _capi.call("rti_rbf_shared_pack_frames", frames.data_ptr() + y * R4, P_loc, N4, rr * R4, packed.data_ptr(), S)
+            _capi.call("rti_rbf_shared_table", packed.data_ptr(), N4, rr * R4, hi.data_ptr(), lo.data_ptr(),
+                       inv.data_ptr(), op_rows, table.data_ptr(), sub_px, sbad.data_ptr(), S)
+
+    shared_ms = timed(run_shared)
+    del packed, hi, lo
+    # (2) per-pixel lights (the reference's semantics): tile-preconditioned CG fit + float32-distance table on
+    # 16 rows of the rank's slab; every pixel is independent and costs the same, so the rank's time is the
+    # sample's time scaled by pixels (sampled, extrapolated)
+    rs = min(16, nr)
+    spx = rs * R4
+    lx = torch.empty((spx, N4), dtype=torch.float32, device="cuda")
+    ly = torch.empty_like(lx)
+    inten = torch.empty((spx, N4), dtype=torch.int32, device="cuda")
+    _capi.call("rti_gather_soa", frames.data_ptr(), P_loc, d_cams.data_ptr(), N4, r0, rs, R4,
+               lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), S)
+    w = torch.empty((spx, N4), dtype=torch.float64, device="cuda")
+    tiles = ((rs + 15) // 16) * (R4 // 16)
+    nbytes = lib.rti_rbf_pcg_workspace_bytes(N4, tiles)
+    work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    iters = torch.empty(spx, dtype=torch.int32, device="cuda")
+    tview = table.view(-1)[:G * G * spx]
+    fit_ms = timed(lambda: (sbad.zero_(), _capi.call(
+        "rti_rbf_fit_pcg", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), rs, R4, N4, w.data_ptr(), work.data_ptr(),
+        nbytes, 48, 0.01, iters.data_ptr(), sbad.data_ptr(), S)))
+    unconv = int(sbad[1].item())
+    ev_ms = timed(lambda: _capi.call("rti_rbf_table_fast", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), spx, N4,
+                                     d_axis.data_ptr(), G, tview.data_ptr(), spx, sbad.data_ptr(), S))
+    # one sampled pixel per rank against scipy's algorithm in fp64
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import rti_oracle as orc
+    q = int(rng.integers(0, spx))
+    l1, l2, dd = lx[q].cpu().numpy(), ly[q].cpu().numpy(), inten[q].cpu().numpy()
+    gref = orc.rbf_grid(l1, l2, orc.rbf_fit(l1, l2, dd), orc.light_axis())
+    ggot = orc.rbf_grid(l1, l2, w[q].cpu().numpy(), orc.light_axis())
+    rbf_rel = float(np.max(np.abs(ggot - gref)) / np.max(np.abs(gref)))
+    steps_mean = float(iters.abs().float().mean().item())
+    op_ms, shared_ms, fit_ms, ev_ms, rbf_rel, unconv_max = max_over_ranks([op_ms, shared_ms, fit_ms, ev_ms, rbf_rel, unconv])
+    pp_s = (fit_ms + ev_ms) * (P_loc / spx) / 1e3
+    n_pad, r_pad = -(-N4 // 64) * 64, -(-op_rows // 128) * 128
+    rbf = {
+        "shared_lights": {"ms": shared_ms, "operator_build_ms": op_ms, "value": P * N4 / (shared_ms * 1e-3) / 1e6,
+                          "unit": UNIT, "executed_tflops_per_gpu": 4.0 * r_pad * n_pad * P_loc / (shared_ms * 1e-3) / 1e12,
+                          "what": "pack + tcgen05 contraction into the int32 table, complete run of the rank's rows"},
+        "per_pixel_lights": {"sample_pixels_per_rank": spx, "fit_ms": fit_ms, "table_ms": ev_ms,
+                             "cg_steps_mean": steps_mean, "unconverged": int(unconv_max),
+                             "extrapolated_full_roi_s": pp_s, "value": P * N4 / pp_s / 1e6, "unit": UNIT,
+                             "grid_max_rel_vs_oracle": rbf_rel,
+                             "what": "pcg fit + float32-distance table on a 16-row sample per rank; sampled, extrapolated"}}
+    del lx, ly, inten, w, work, iters
     out = {"workload": "synthetic 4096x4096 ROI x 1000 light samples, PTM fit + 100x100 light grid (BASELINE configs[3])",
            "scaling": "strong", "ranks": world, "rows_per_rank": nr, "sub_slab_rows": SUB,
            "ptm_ms": ptm_ms, "gather_ms": gather_ms, "total_ms": total_ms,
@@ -472,7 +558,8 @@ def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
            "roofline": {"bound": "hbm", "achieved": alg / world / (ptm_ms * 1e-3) / 1e9, "peak": hbm_peak,
                         "frac": alg / world / (ptm_ms * 1e-3) / 1e9 / hbm_peak, "unit": "GB/s per GPU"},
            "parity_sample": {"pixels_per_rank": 12, "max_rel": float(par[0].item()),
-                             "table_mismatch": int(par[1].item()), "singular": int(par[2].item())}}
+                             "table_mismatch": int(par[1].item()), "singular": int(par[2].item())},
+           "rbf": rbf}
     del frames, coef, table, full
     torch.cuda.empty_cache()
     return out
