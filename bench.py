@@ -441,6 +441,17 @@ def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ptm_ms, gather_ms, total_ms = [float(v) for v in t.tolist()]
+    # the gather alone, all ranks released together (gather_ms above also contains the wait for the slowest rank)
+    ga = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    barrier()
+    ga[0].record()
+    full = sharding.gather_planar(coef, R4, R4, dst=0) if dist is not None else coef
+    ga[1].record()
+    barrier()
+    t = torch.tensor([ga[0].elapsed_time(ga[1])], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    gather_alone_ms = float(t.item())
     nbad = int(bad.sum().item())
     # sampled oracle check: coefficients anywhere in the slab, table columns in the last sub-slab
     rng = np.random.default_rng(7 + rank)
@@ -553,7 +564,8 @@ def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
            "ptm_ms": ptm_ms, "gather_ms": gather_ms, "total_ms": total_ms,
            "value": P * N4 / (total_ms * 1e-3) / 1e6, "unit": UNIT,
            "nccl_gather_bytes": gather_bytes,
-           "nccl_gather_gbs": (gather_bytes / (gather_ms * 1e-3) / 1e9) if world > 1 else None,
+           "gather_alone_ms": gather_alone_ms,
+           "nccl_gather_gbs": (gather_bytes / (gather_alone_ms * 1e-3) / 1e9) if world > 1 else None,
            "gather": "fp64 coefficient map (6, rows, cols) to rank 0, sharding.gather_planar (batch_isend_irecv)",
            "roofline": {"bound": "hbm", "achieved": alg / world / (ptm_ms * 1e-3) / 1e9, "peak": hbm_peak,
                         "frac": alg / world / (ptm_ms * 1e-3) / 1e9 / hbm_peak, "unit": "GB/s per GPU"},

@@ -240,3 +240,45 @@ def test_write_on_file_falls_back_when_the_template_does_not_apply(tmp_path, mon
     with open(name + ".pickle", "rb") as f:
         back = pickle.load(f)
     assert np.array_equal(np.array(back), table)
+
+
+def test_table_tile_writer_equals_pickle_dump(tmp_path):
+    """TableTileWriter lays the result pickle out up front and drops ROW TILES of every image at fixed
+    offsets (what compute() does with device tiles); the file must be byte-identical to the streaming
+    writer's and un-pickle to the reference's object graph (analysis.py:400-409, 475)."""
+    import pickle
+    from rti_b200 import table_io
+    rng = np.random.default_rng(3)
+    gv, gu, rows, cols = 3, 4, 9, 5
+    table = rng.integers(-2 ** 31, 2 ** 31 - 1, (gv, gu, rows, cols)).astype(np.int32)
+    path = str(tmp_path / "tiles.pickle")
+    w = table_io.TableTileWriter(gv, gu, (rows, cols), np.int32, path)
+    flat = table.reshape(gv * gu, rows, cols)
+    for r0, tr in ((4, 3), (0, 4), (7, 2)):                      # tiles in any order
+        for i0, cnt in ((0, 5), (5, 7)):                         # image chunks as the pinned ring delivers them
+            w.write_rows(i0, flat[i0:i0 + cnt, r0:r0 + tr].reshape(cnt, -1), r0)
+    w.close()
+    with open(path, "rb") as f:
+        raw = f.read()
+    assert raw == table_io.dumps_table(table)
+    back = pickle.loads(raw)
+    assert len(back) == gv and len(back[0]) == gu
+    assert all(np.array_equal(back[v][u], table[v, u]) and back[v][u].flags.writeable
+               for v in range(gv) for u in range(gu))
+    mapped = table_io.load_table(path)
+    assert mapped is not None and np.array_equal(mapped[2][3], table[2, 3])
+
+
+def test_rbf_pcg_entry_validates_arguments_without_gpu(lib):
+    import ctypes as C
+    from rti_b200 import _capi
+    assert lib.rti_rbf_pcg_workspace_bytes(2, 1) == 0 and lib.rti_rbf_pcg_workspace_bytes(1026, 1) == 0
+    one, two = lib.rti_rbf_pcg_workspace_bytes(500, 1), lib.rti_rbf_pcg_workspace_bytes(500, 2)
+    assert 0 < one < two and one % 256 == 0
+    buf = (C.c_double * 64)()
+    p = C.cast(buf, C.c_void_p)
+    assert lib.rti_rbf_fit_pcg(None, p, p, 4, 4, 40, p, p, one, 8, 0.01, None, None, None) == _capi.RTI_ERR_ARG
+    assert lib.rti_rbf_fit_pcg(p, p, p, 4, 4, 2, p, p, one, 8, 0.01, None, None, None) == _capi.RTI_ERR_ARG   # n < 3
+    assert lib.rti_rbf_fit_pcg(p, p, p, 4, 4, 40, p, p, 1024, 8, 0.01, None, None, None) == _capi.RTI_ERR_ARG  # workspace
+    assert lib.rti_rbf_fit_pcg(p, p, p, 4, 4, 40, p, p, one, 0, 0.01, None, None, None) == _capi.RTI_ERR_ARG   # max_iters
+    assert lib.rti_rbf_table_fast(p, p, p, 0, 40, p, 100, p, 4, None, None) == _capi.RTI_ERR_ARG

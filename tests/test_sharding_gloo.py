@@ -31,6 +31,12 @@ def _worker(rank, world, port, rows, cols, out_path):
         x = torch.arange(cols, dtype=torch.float64).view(1, 1, cols)
         local = (k + y + x).reshape(6, nr * cols)
         full = sharding.gather_planar(local, rows, cols, dst=0)
+        if rows % world == 0 and rows > 0:
+            # the all-gather form (equal slabs) gives the same map
+            full2 = sharding.gather_planar(local, rows, cols, dst=0, method="allgather")
+            assert (full2 is None) == (rank != 0)
+            if rank == 0:
+                assert torch.equal(full, full2)
         if rank == 0:
             np.save(out_path, full.numpy())
         else:
