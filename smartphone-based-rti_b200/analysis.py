@@ -490,14 +490,17 @@ def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
                    coef.data_ptr(), n_pixels, bad.data_ptr(), _stream_ptr(torch))
         _raise_if_bad(bad, "PTM")
         return InterpolationResult("ptm", range_val, range_val, axis, coef=coef)
-    if lights_are_shared(lx, ly):
-        # one light vector per frame for the whole ROI: one operator, one tensor-core contraction
-        res = InterpolationResult("rbf_shared", range_val, range_val, axis)
+    precision = RBF_PRECISION if RBF_PRECISION in ("fast", "fp64") else "fast"
+    if precision == "fast" and lights_are_shared(lx, ly):
+        # one light vector per frame for the whole ROI: one operator, one tensor-core contraction (fp16 hi+lo
+        # operator: grid values within ~2e-5 of the maximum; RBF_PRECISION = "fp64" keeps such data on the
+        # per-pixel fp64 kernels)
+        res = InterpolationResult("rbf_shared", range_val, range_val, axis, precision="fast",
+                                  path="rbf: shared lights, one tcgen05 contraction (fp16 hi+lo operator)")
         res.shared = SharedLightRbf(lx[0].clone(), ly[0].clone(), axis, res.d_axis())
         if res.shared.pack_soa(inten):     # intensities exact in fp16 (always true for uint8 frames)
             res.shared.operator(0)
             return res
-    precision = RBF_PRECISION if RBF_PRECISION in ("fast", "fp64") else "fast"
     if precision == "fast" and 3 <= n <= 1025:
         weights, info = rbf_fit_device_pcg(lx, ly, inten, range_val, range_val, bad)
         path = "rbf: pcg fit (%d of %d pixels refitted directly) + float32-distance table" % (info["refit"], n_pixels)

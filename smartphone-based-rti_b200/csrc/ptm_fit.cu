@@ -278,6 +278,12 @@ constexpr int SH_THREADS = 128;
 constexpr int SH_CHUNK = 256;
 constexpr int SH_UNROLL = 16;
 
+// Measured variants (262 144 px x 500 lights, tools/prof_shared_fit.py; ncu of this form: fp64 pipe 45 %,
+// warps active 18 %, stalled on the frame loads): this form (4 pixels per thread, 16 loads in flight) 0.133 ms =
+// 0.32 of the DFMA peak, 0.45 at 1 M pixels; frames split over the 8 warps of a CTA with a shared-memory
+// reduction (4x the threads) 0.195 ms; 2 pixels per thread 0.133 / 0.426 ms, 1 pixel 0.150 / 0.512 ms: more
+// threads do not help, the pinv LDS per DFMA and the byte unpacking grow instead.  Kept as is.
+
 __global__ void __launch_bounds__(SH_THREADS)
 ptm_fit_shared_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
                       const double *__restrict__ pinv, int n, int64_t n_pixels,
