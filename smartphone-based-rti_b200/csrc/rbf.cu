@@ -655,7 +655,9 @@ extern "C" int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const do
     static const int variant = getenv("RTI_RBF_FAST_VARIANT") ? atoi(getenv("RTI_RBF_FAST_VARIANT")) : 0;
     // development A/B (tools/prof_rbf.py, N = 500, 4736 pixels): <8,4> 6.94 ms, <4,10> 7.14, <8,5> 6.84,
     // <2,10> 6.62, <4,4> 6.55 ms = 0.78 of the SFU peak (ncu: XU pipe 80 %, issue slots 76 %, stalls = MIO
-    // throttle, i.e. the MUFU queue is full); 0 is the shipped shape
+    // throttle, i.e. the MUFU queue is full); 0 is the shipped shape.  Also measured and dropped: MUFU.RSQ + FMUL
+    // instead of MUFU.SQRT 7.30 ms (one more issue slot per term); register caps for 4 / 5 CTAs per SM
+    // (64 / 48 registers) 7.13 / 7.47 ms; <2,8> at 64 registers 7.89 ms; <4,8> 7.66 ms
     switch (variant) {
     case 1: return rbf_fast_launch<8, 4>(RTI_FAST_ARGS);
     case 2: return rbf_fast_launch<2, 10>(RTI_FAST_ARGS);
