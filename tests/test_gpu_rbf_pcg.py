@@ -94,3 +94,49 @@ def test_pcg_reports_unconverged_pixels(torch_cuda):
     _, iters, bad = fit_pcg(torch_cuda, lx, ly, inten, max_iters=2)
     assert bad[0] == 0 and bad[1] > 0
     assert bad[1] == np.count_nonzero(iters < 0) and np.all(np.abs(iters) <= 2)
+
+
+def _py_fit(torch, lx, ly, inten, **kw):
+    from rti_b200 import analysis
+    rows, cols, n = lx.shape
+    d = [torch.from_numpy(np.ascontiguousarray(a.reshape(rows * cols, n))).cuda() for a in (lx, ly, inten)]
+    bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+    w, info = analysis.rbf_fit_device_pcg(d[0], d[1], d[2], rows, cols, bad, **kw)
+    torch.cuda.synchronize()
+    return w.cpu().numpy().reshape(rows, cols, n), info, int(bad.item())
+
+
+def test_pcg_unrelated_neighbours_are_refitted_directly(torch_cuda):
+    """Data whose neighbouring pixels do NOT have similar nodes (arbitrary arrays handed to
+    interpolate_intensities): the tile-centre preconditioner is useless, the host layer refits what did
+    not converge with the direct fp64 kernel, and every pixel still matches the oracle."""
+    rng = np.random.default_rng(3)
+    rows, cols, n = 16, 20, 60
+    r = np.sqrt(rng.uniform(0, 0.95, (rows, cols, n)))
+    th = rng.uniform(0, 2 * np.pi, (rows, cols, n))
+    lx, ly = (r * np.cos(th)).astype(np.float32), (r * np.sin(th)).astype(np.float32)
+    inten = rng.integers(0, 256, (rows, cols, n)).astype(np.int32)
+    w, info, bad = _py_fit(torch_cuda, lx, ly, inten, max_iters=12)
+    assert bad == 0 and info["refit"] > rows * cols // 2
+    check_pixels(lx, ly, inten, w, [(0, 0), (8, 8), (15, 19), (3, 17), (12, 1)], node_atol=0.06)
+
+
+def test_pcg_singular_tile_centre_and_singular_pixel(torch_cuda):
+    """Duplicate nodes (scipy: LinAlgError) at a tile CENTRE leave that tile without a preconditioner: its
+    pixels are refitted directly and only the genuinely singular pixels are counted."""
+    lx, ly, inten = slab(16, 32, 50, seed=4)
+    lx, ly = lx.copy(), ly.copy()
+    lx[8, 8, 7], ly[8, 8, 7] = lx[8, 8, 3], ly[8, 8, 3]              # centre of tile 0
+    lx[2, 20, 9], ly[2, 20, 9] = lx[2, 20, 0], ly[2, 20, 0]          # an ordinary pixel of tile 1
+    w, info, bad = _py_fit(torch_cuda, lx, ly, inten)
+    assert info["singular_tiles"] == 1 and bad == 2
+    assert info["refit"] >= 256
+    ok = [(0, 0), (8, 9), (15, 15), (0, 31), (9, 24)]
+    check_pixels(lx, ly, inten, w, ok, node_atol=0.06)
+
+
+def test_pcg_largest_supported_n(torch_cuda):
+    lx, ly, inten = slab(16, 16, 1025, seed=6, lambert=True)
+    w, iters, bad = fit_pcg(torch_cuda, lx, ly, inten, max_iters=120)
+    assert bad.tolist() == [0, 0]
+    check_pixels(lx, ly, inten, w, [(0, 0), (9, 7)], node_atol=0.06)
