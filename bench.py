@@ -359,6 +359,47 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
     return res
 
 
+# ------------------------------------------- BASELINE configs[4]: relighting frames per second
+def relight_config5(torch, lib, _capi, hbm_peak):
+    """4096 x 4096 PTM coefficient map re-rendered for a sweep of 1000 light directions (the headless
+    relighting_event, interactive_relighting.py:11-39): frames/s on one GPU from the fp64 map (bit-identical to
+    the table at grid nodes) and the fp32 map, V channel only and with the fused OpenCV HSV->BGR."""
+    R = 4096
+    p = R * R
+    S = torch.cuda.current_stream().cuda_stream
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    c64 = torch.randn((6, p), dtype=torch.float64, device="cuda", generator=gen) * 40.0
+    c32 = torch.empty((6, p), dtype=torch.float32, device="cuda")
+    _capi.call("rti_coef_to_f32", c64.data_ptr(), 6 * p, c32.data_ptr(), S)
+    hsv = torch.randint(0, 180, (R, R, 3), dtype=torch.uint8, device="cuda", generator=gen)
+    dirs = np.random.default_rng(1).uniform(-1, 1, (1000, 2))
+    out = {"workload": "4096x4096 PTM coefficient map, 1000 light directions", "frames": len(dirs)}
+    for name, fn, cmap, cbytes in (("f64", "rti_relight_ptm", c64, 48), ("f32", "rti_relight_ptm_f32", c32, 24)):
+        for label, hsv_t, obytes in (("V", None, 1), ("bgr", hsv, 6)):
+            o = torch.empty((R, R, 3) if hsv_t is not None else (R, R), dtype=torch.uint8, device="cuda")
+            hp = hsv_t.data_ptr() if hsv_t is not None else None
+
+            def sweep():
+                for lu, lv in dirs:
+                    _capi.call(fn, cmap.data_ptr(), p, p, R, float(lu), float(lv), hp, o.data_ptr(), S)
+
+            for lu, lv in dirs[:20]:
+                _capi.call(fn, cmap.data_ptr(), p, p, R, float(lu), float(lv), hp, o.data_ptr(), S)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            sweep()
+            b.record()
+            torch.cuda.synchronize()
+            ms = a.elapsed_time(b) / len(dirs)
+            gbs = (cbytes + obytes) * p / (ms * 1e-3) / 1e9
+            out["%s_%s" % (name, label)] = {"frames_per_s": 1e3 / ms, "ms_per_frame": ms, "achieved_gbs": gbs,
+                                            "frac_of_hbm": gbs / hbm_peak}
+    out["note"] = ("every frame re-reads the whole map (403 / 805 MB > L2); bound = HBM read; a real-time display "
+                   "needs 60 frames/s")
+    return out
+
+
 # ------------------------------------------------------------------ parity sample (checker)
 def parity_sample(frames_of, cams, row0, cols, n_pixels, coef_cols, table_cols, idx):
     """Holds sampled pixels of a finished run to the CPU oracle (the checker, after the timed region):
@@ -757,6 +798,11 @@ def run_gpu(args, rank, local_rank, world):
         if cpu_rbf is not None:
             secondary["rbf_per_pixel_lights"]["cpu_baseline"] = cpu_rbf
             secondary["rbf_per_pixel_lights"]["vs_cpu"] = secondary["rbf_per_pixel_lights"]["value"] / cpu_rbf["value"]
+    relight = None
+    if world == 1 and not args.no_secondary:
+        d_table = d_coef = d_frames = None
+        torch.cuda.empty_cache()
+        relight = relight_config5(torch, lib, _capi, read_peaks()[0])
     config4 = None
     if not args.no_config4:
         d_table = d_coef = d_frames = None                          # release the headline buffers
@@ -789,7 +835,7 @@ def run_gpu(args, rank, local_rank, world):
         "config": make_config(world),
         "e2e": e2e, "parity_sample": parity, "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "kernel_ms": {"ptm_fused": fused_ms, "ptm_fit_frames": fit_ms, "ptm_table": table_ms},
-        "secondary": secondary, "config4": config4,
+        "secondary": secondary, "config5_relight": relight, "config4": config4,
     }
     return line
 
