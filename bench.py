@@ -235,7 +235,10 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
 
     res = {}
     bad = torch.zeros(2, dtype=torch.int32, device="cuda")
-    sm_peak = 148 * 16 * 1.965e9                 # square roots per second: 16 per clock per SM
+    # square roots per second: 16 per clock per SM = 4.65e12 nominal; this repo's microbenchmark
+    # (tools/peak_sfu.cu, profiles/r02_peak_sfu.jsonl) sustains 4.62e12 with MUFU alone and 4.14e12 with the
+    # evaluation kernel's instruction mix on register operands
+    sm_peak = 4.62e12
     # ---- per-pixel lights (the reference's semantics), default "fast" path: rows [0, 256) of the slab
     rows_s = 256
     px = rows_s * COLS
@@ -290,8 +293,9 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
         "roofline": {"bound": "sfu", "kernel": "rbf_eval_f32_kernel",
                      "achieved": G * G * N_LIGHTS * px / (ev_ms * 1e-3) / 1e12, "peak": sm_peak / 1e12,
                      "unit": "Tsqrt/s", "frac": G * G * N_LIGHTS * px / (ev_ms * 1e-3) / sm_peak,
-                     "note": "G*G*N square roots per pixel on MUFU; peak = 148 SM x 16 per clock x 1.965 GHz "
-                             "(nominal SFU rate; MEASURED_PEAKS.json has no SFU figure)"},
+                     "note": "G*G*N square roots per pixel on MUFU; peak = the SFU rate this repo's own microbenchmark "
+                             "sustains (tools/peak_sfu.cu: 4.62 T/s = 16 per clock per SM; 4.14 T/s with this "
+                             "kernel's instruction mix); MEASURED_PEAKS.json has no SFU figure"},
         "parity_sample": {"pixels": int(len(sample_px)), "grid_max_rel": worst, "tolerance": 1e-3,
                           "table_entries_off_beyond_tolerance": flips},
         "singular_tiles": singular_tiles, "unrepresentable": int(bad[0].item())}
