@@ -516,8 +516,8 @@ rbf_pcg_init_kernel(const float *__restrict__ lx, const float *__restrict__ ly, 
 }
 
 // One conjugate-gradient step of both systems of one pixel.  ROWS = rows of the matrix per thread.
-template <int ROWS>
-__global__ void __launch_bounds__(PCG_THREADS)
+template <int ROWS, int MINB>
+__global__ void __launch_bounds__(PCG_THREADS, MINB)
 rbf_pcg_step_kernel(const float *__restrict__ lx, const float *__restrict__ ly, PcgGeom g, PcgState st, int iter,
                     double tol0, double tol1) {
     extern __shared__ __align__(16) unsigned char pcg_smem[];
@@ -534,51 +534,51 @@ rbf_pcg_step_kernel(const float *__restrict__ lx, const float *__restrict__ ly, 
     const int k_rows = 2 * g.k_pad;
     const float x0 = lx[pix * n], y0 = ly[pix * n];
 
-    double a[ROWS], z0[ROWS], z1[ROWS], r0[ROWS], r1[ROWS];
+    double z0[ROWS], z1[ROWS];
     float xj[ROWS], yj[ROWS];
     const float zs0 = st.zscale[col0], zs1 = st.zscale[col1];
     double red[4] = {0.0, 0.0, 0.0, 0.0};
 #pragma unroll
     for (int i = 0; i < ROWS; ++i) {
         const int j = t + i * PCG_THREADS;
-        a[i] = z0[i] = z1[i] = r0[i] = r1[i] = 0.0;
+        z0[i] = z1[i] = 0.0;
         xj[i] = yj[i] = 0.f;
+        double r0 = 0.0, r1 = 0.0;
         if (j < M) {
             xj[i] = lx[pix * n + j + 1];
             yj[i] = ly[pix * n + j + 1];
-            a[i] = widen_pos(dist_f32(xj[i], yj[i], x0, y0));
             z0[i] = st.Z[col0 * r_pad + j] * (double)zs0;
             z1[i] = st.Z[col1 * r_pad + j] * (double)zs1;
-            r0[i] = st.R[col0 * r_pad + j];
-            r1[i] = st.R[col1 * r_pad + j];
+            r0 = st.R[col0 * r_pad + j];
+            r1 = st.R[col1 * r_pad + j];
         }
         if (j < r_pad) s_xy[j] = make_float2(xj[i], yj[i]);
-        red[0] = fma(r0[i], z0[i], red[0]);
-        red[1] = fma(r1[i], z1[i], red[1]);
+        red[0] = fma(r0, z0[i], red[0]);
+        red[1] = fma(r1, z1[i], red[1]);
     }
     block_reduce<2, false>(reinterpret_cast<double(&)[2]>(red), s_red);
     const double rz0 = red[0], rz1 = red[1];
     const double rzo0 = st.rz[col0], rzo1 = st.rz[col1];
     const double beta0 = (iter > 0 && rzo0 != 0.0) ? rz0 / rzo0 : 0.0;
     const double beta1 = (iter > 0 && rzo1 != 0.0) ? rz1 / rzo1 : 0.0;
-    double p0[ROWS], p1[ROWS];
     red[0] = red[1] = red[2] = red[3] = 0.0;
 #pragma unroll
     for (int i = 0; i < ROWS; ++i) {
         const int j = t + i * PCG_THREADS;
-        p0[i] = p1[i] = 0.0;
+        double p0 = 0.0, p1 = 0.0, aj = 0.0;
         if (j < M) {
             // the direction is rounded to float32 ONCE and used rounded everywhere
-            p0[i] = (double)(float)fma(beta0, (double)st.Pv[col0 * r_pad + j], z0[i]);
-            p1[i] = (double)(float)fma(beta1, (double)st.Pv[col1 * r_pad + j], z1[i]);
-            st.Pv[col0 * r_pad + j] = (float)p0[i];
-            st.Pv[col1 * r_pad + j] = (float)p1[i];
+            p0 = (double)(float)fma(beta0, (double)st.Pv[col0 * r_pad + j], z0[i]);
+            p1 = (double)(float)fma(beta1, (double)st.Pv[col1 * r_pad + j], z1[i]);
+            st.Pv[col0 * r_pad + j] = (float)p0;
+            st.Pv[col1 * r_pad + j] = (float)p1;
+            aj = widen_pos(dist_f32(xj[i], yj[i], x0, y0));
         }
-        if (j < r_pad) s_p[j] = make_double2(p0[i], p1[i]);
-        red[0] += p0[i];
-        red[1] += p1[i];
-        red[2] = fma(a[i], p0[i], red[2]);
-        red[3] = fma(a[i], p1[i], red[3]);
+        if (j < r_pad) s_p[j] = make_double2(p0, p1);
+        red[0] += p0;
+        red[1] += p1;
+        red[2] = fma(aj, p0, red[2]);
+        red[3] = fma(aj, p1, red[3]);
     }
     block_reduce<4, false>(red, s_red);                              // (also publishes s_p / s_xy)
     const double S1_0 = red[0], S1_1 = red[1], S2_0 = red[2], S2_1 = red[3];
@@ -587,6 +587,12 @@ rbf_pcg_step_kernel(const float *__restrict__ lx, const float *__restrict__ ly, 
     double acc0[ROWS], acc1[ROWS];
 #pragma unroll
     for (int i = 0; i < ROWS; ++i) acc0[i] = acc1[i] = 0.0;
+    // Where a step's time goes (ncu + timing experiments at n = 500, 16 384 pixels, 1.73 ms per step): the sweep
+    // is 88 % of the instructions and issue-bound (stall = not selected; 1.19 ms at one instruction per clock per
+    // scheduler, the same as its SFU time at the 78 % the evaluation kernel reaches); everything else alone takes
+    // 0.26 ms (the step without the sweep: 3.4 TB/s of vector traffic).  Without the square root 1.57 ms, with
+    // one system only 1.56 ms, packed FADD2 / FMUL2 / FFMA2 for the float32 part: no change (they issue at half
+    // rate); 5 or 6 CTAs per SM instead of 4: -1.6 %.
 #pragma unroll 4
     for (int k = 0; k < M; ++k) {
         const float2 xy = s_xy[k];
@@ -598,32 +604,40 @@ rbf_pcg_step_kernel(const float *__restrict__ lx, const float *__restrict__ ly, 
             acc1[i] = fma(r, pk.y, acc1[i]);
         }
     }
-    // q = B p = a (1.p) + (a.p) 1 - A' p ; alpha = rz / p.q
-    double q0[ROWS], q1[ROWS];
+    // q = B p = a (1.p) + (a.p) 1 - A' p ; alpha = rz / p.q.  a, p and r are re-derived here (node 0 distance,
+    // shared memory, L2) instead of being kept in registers across the sweep: the sweep then needs 40 registers
+    // and six CTAs fit on an SM, whose load / reduction phases hide behind one another's sweeps.
+    double q0[ROWS], q1[ROWS], pa[ROWS], pb[ROWS];
     red[0] = red[1] = 0.0;
 #pragma unroll
     for (int i = 0; i < ROWS; ++i) {
         const int j = t + i * PCG_THREADS;
-        q0[i] = q1[i] = 0.0;
+        q0[i] = q1[i] = pa[i] = pb[i] = 0.0;
         if (j < M) {
-            q0[i] = fma(a[i], S1_0, S2_0) - acc0[i];
-            q1[i] = fma(a[i], S1_1, S2_1) - acc1[i];
+            const double aj = widen_pos(dist_f32(xj[i], yj[i], x0, y0));
+            const double2 pj = s_p[j];
+            pa[i] = pj.x;
+            pb[i] = pj.y;
+            q0[i] = fma(aj, S1_0, S2_0) - acc0[i];
+            q1[i] = fma(aj, S1_1, S2_1) - acc1[i];
         }
-        red[0] = fma(p0[i], q0[i], red[0]);
-        red[1] = fma(p1[i], q1[i], red[1]);
+        red[0] = fma(pa[i], q0[i], red[0]);
+        red[1] = fma(pb[i], q1[i], red[1]);
     }
     block_reduce<2, false>(reinterpret_cast<double(&)[2]>(red), s_red);
     const double al0 = (red[0] > 0.0) ? rz0 / red[0] : 0.0;
     const double al1 = (red[1] > 0.0) ? rz1 / red[1] : 0.0;
     red[0] = red[1] = 0.0;
+    double r0[ROWS], r1[ROWS];
 #pragma unroll
     for (int i = 0; i < ROWS; ++i) {
         const int j = t + i * PCG_THREADS;
+        r0[i] = r1[i] = 0.0;
         if (j < M) {
-            st.X[col0 * r_pad + j] = fma(al0, p0[i], st.X[col0 * r_pad + j]);
-            st.X[col1 * r_pad + j] = fma(al1, p1[i], st.X[col1 * r_pad + j]);
-            r0[i] = fma(-al0, q0[i], r0[i]);
-            r1[i] = fma(-al1, q1[i], r1[i]);
+            st.X[col0 * r_pad + j] = fma(al0, pa[i], st.X[col0 * r_pad + j]);
+            st.X[col1 * r_pad + j] = fma(al1, pb[i], st.X[col1 * r_pad + j]);
+            r0[i] = fma(-al0, q0[i], st.R[col0 * r_pad + j]);
+            r1[i] = fma(-al1, q1[i], st.R[col1 * r_pad + j]);
             st.R[col0 * r_pad + j] = r0[i];
             st.R[col1 * r_pad + j] = r1[i];
         }
@@ -813,12 +827,12 @@ extern "C" int rti_rbf_fit_pcg(const float *d_lx, const float *d_ly, const int32
                                       L.k_pad, 2, st.Z, st.tile_active, s);
             if (rc != RTI_OK) return rc;
 #define RTI_PCG_STEP(R)                                                                                            \
-    rbf_pcg_step_kernel<R><<<dim3(PTILE, T), PCG_THREADS, step_smem, s>>>(d_lx, d_ly, g, st, it, tol, tol1)
+    rbf_pcg_step_kernel<R, MB><<<dim3(PTILE, T), PCG_THREADS, step_smem, s>>>(d_lx, d_ly, g, st, it, tol, tol1)
             switch (rows_per_thread) {
-            case 1: RTI_PCG_STEP(1); break;
-            case 2: RTI_PCG_STEP(2); break;
-            case 3: RTI_PCG_STEP(3); break;
-            default: RTI_PCG_STEP(4); break;
+            case 1: { constexpr int MB = 6; RTI_PCG_STEP(1); } break;
+            case 2: { constexpr int MB = 6; RTI_PCG_STEP(2); } break;
+            case 3: { constexpr int MB = 3; RTI_PCG_STEP(3); } break;
+            default: { constexpr int MB = 2; RTI_PCG_STEP(4); } break;
             }
 #undef RTI_PCG_STEP
             RTI_LAUNCHED("rbf_pcg_step_kernel");
