@@ -86,6 +86,64 @@ constexpr uint32_t IDESC = (1u << 4) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) 
 constexpr uint32_t IDESC_BK = IDESC & ~(1u << 16);      // B K-major as well (batched form: vectors stored [column][k])
 
 
+// ---- CTA-pair form (tcgen05 cta_group::2) --------------------------------------------------
+// Two CTAs of a cluster (the two SMs of a TPC) work on one 256-row x 256-pixel tile: each CTA stages ITS 128
+// operator rows (hi and lo) and ITS half of the intensity tile (128 pixels), the leader's single thread issues
+// M = 256 MMAs that read both halves, every CTA's TMEM receives its 128 rows of the accumulator.  Per CTA the
+// intensity operand is filled and read at half the rate of the single-CTA kernel, which is what that kernel is
+// short of (shared-memory bandwidth: TMA fill + operand reads + epilogue staging against 128 B/clk), and a stage
+// shrinks from 64 KB to 48 KB: four stages instead of three.
+constexpr int STAGES2 = 4;
+constexpr int B_HALF = (BN / 2 / 64) * B_BOX;              // 16 KB
+constexpr int STAGE2_BYTES = 2 * A_TILE + B_HALF;          // 48 KB
+constexpr int SMEM2_BYTES = STAGES2 * STAGE2_BYTES + EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr uint32_t IDESC2 = (1u << 4) | (1u << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t map_to_cta(uint32_t smem_addr, uint32_t rank) {     // shared::cluster address
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// TMA loads whose completion bytes are counted on a barrier of the pair's leader CTA
+__device__ __forceinline__ void tma2_load_2d(uint32_t dst, const CUtensorMap *map, int c0, int c1, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma2_load_3d(uint32_t dst, const CUtensorMap *map, int c0, int c1, int c2, uint32_t bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+__device__ __forceinline__ void tc2_commit(uint32_t bar) {        // arrives on `bar` of BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3)
+                 : "memory");
+}
+__device__ __forceinline__ void tc2_mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                            uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
 // ---- the contraction --------------------------------------------------------------------
 struct GemmArgs {
     int op_rows;               // R: rows of the operator (G*G for the table, N for weights)
@@ -284,10 +342,19 @@ rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_
                             chunk_parity ^= 1;
                         }
                     } else {
+                        int32_t *dst = args.table + (long long)row * args.image_stride + p0;
+                        if (row_ok && p0 + 32 <= args.n_pixels && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                            // a lane owns one row: 32 consecutive pixels = one 128-byte line, as 8 streaming 16-byte stores
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) {
-                            const long long p = p0 + j;
-                            if (row_ok && p < args.n_pixels) args.table[(long long)row * args.image_stride + p] = iv[j];
+                            for (int j = 0; j < 8; ++j)
+                                __stcs(reinterpret_cast<int4 *>(dst) + j,
+                                       make_int4(iv[4 * j], iv[4 * j + 1], iv[4 * j + 2], iv[4 * j + 3]));
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const long long p = p0 + j;
+                                if (row_ok && p < args.n_pixels) dst[j] = iv[j];
+                            }
                         }
                     }
                 }
@@ -304,6 +371,206 @@ rbf_shared_gemm_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_
     if (warp == 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS)
+                     : "memory");
+    }
+}
+
+
+// CTA-pair variant of rbf_shared_gemm_kernel (shared-light tables; B MN-major).  Barrier protocol:
+//   full[s]   leader only: one arrival (the leader's expect_tx of both CTAs' bytes); both CTAs' TMA loads
+//             complete on it;          empty[s]  per CTA: the leader's commit arrives on both (multicast);
+//   tfull[a]  per CTA: commit multicast; tempty[a] leader only: 8 arrivals, one per epilogue warp of both CTAs.
+template <int MODE>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1)
+rbf_shared_gemm2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
+                        const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_out,
+                        const GemmArgs args) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t epi_base = base + STAGES2 * STAGE2_BYTES;
+    const uint32_t bar_base = epi_base + EPI_BYTES;
+    const uint32_t bar_full = bar_base, bar_empty = bar_base + 8 * STAGES2;
+    const uint32_t bar_tfull = bar_base + 16 * STAGES2, bar_tempty = bar_tfull + 16;
+    const uint32_t tmem_slot = bar_tempty + 16;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_rank();
+    const bool leader = rank == 0;
+    const int num_k = (args.n + BK - 1) / BK;
+    const int num_m2 = (args.num_m_blks + 1) / 2;                    // 256-row blocks
+    const int num_tiles = num_m2 * args.num_n_blks;
+    const int cluster_id = blockIdx.x >> 1, num_clusters = gridDim.x >> 1;
+
+    if (warp == 0 && lane == 0) {
+        prefetch_tmap(&map_hi);
+        prefetch_tmap(&map_lo);
+        prefetch_tmap(&map_b);
+        if (MODE == STORE_TMA) prefetch_tmap(&map_out);
+        for (int s = 0; s < STAGES2; ++s) {
+            mbar_init(bar_full + 8 * s, 1);
+            mbar_init(bar_empty + 8 * s, 1);
+        }
+        for (int a = 0; a < 2; ++a) {
+            mbar_init(bar_tfull + 8 * a, 1);
+            mbar_init(bar_tempty + 8 * a, 8);      // four epilogue warps of each CTA
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                     "r"((uint32_t)TMEM_COLS)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    cluster_sync_all();                            // both CTAs' barriers initialised, both allocations done
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot) : "memory");
+
+    if (warp == 0) {
+        // ===== TMA producer (both CTAs): own 128 operator rows, own 128 pixels =====
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                const int m2 = tile % num_m2, n_blk = tile / num_m2;
+                const int a_row = m2 * 2 * BM + (int)rank * BM;
+                for (int kb = 0; kb < num_k; ++kb) {
+                    mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                    const uint32_t full = map_to_cta(bar_full + 8 * stage, 0);       // the leader's barrier
+                    const uint32_t sa = base + stage * STAGE2_BYTES;
+                    if (leader) mbar_expect_tx(bar_full + 8 * stage, 2 * STAGE2_BYTES);
+                    tma2_load_2d(sa, &map_hi, kb * BK, a_row, full);
+                    tma2_load_2d(sa + A_TILE, &map_lo, kb * BK, a_row, full);
+#pragma unroll
+                    for (int j = 0; j < BN / 2 / 64; ++j)
+                        tma2_load_3d(sa + 2 * A_TILE + j * B_BOX, &map_b, ((int)rank * (BN / 2 / 64) + j) * 64, kb * BK,
+                                     n_blk, full);
+                    if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer: one thread of the LEADER drives both SMs' tensor cores =====
+        if (lane == 0 && leader) {
+            int stage = 0, acc = 0;
+            uint32_t phase = 0, aphase = 0;
+            for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+                mbar_wait(bar_tempty + 8 * acc, aphase ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + acc * BN;
+                for (int kb = 0; kb < num_k; ++kb) {
+                    mbar_wait(bar_full + 8 * stage, phase);
+                    tc_fence_after();
+                    const uint32_t sa = base + stage * STAGE2_BYTES;
+#pragma unroll
+                    for (int k = 0; k < BK / UK; ++k) {
+                        const uint64_t da_hi = smem_desc(sa + k * (UK * 2), 16, 1024);
+                        const uint64_t da_lo = smem_desc(sa + A_TILE + k * (UK * 2), 16, 1024);
+                        const uint64_t db = smem_desc(sa + 2 * A_TILE + k * (UK * 128), B_BOX, 1024);
+                        tc2_mma_f16(d_tmem, da_hi, db, IDESC2, (kb | k) != 0);
+                        tc2_mma_f16(d_tmem, da_lo, db, IDESC2, 1u);
+                    }
+                    tc2_commit(bar_empty + 8 * stage);             // both CTAs' slots free once these MMAs retire
+                    if (kb == num_k - 1) tc2_commit(bar_tfull + 8 * acc);
+                    if (++stage == STAGES2) { stage = 0; phase ^= 1; }
+                }
+                acc ^= 1;
+                if (acc == 0) aphase ^= 1;
+            }
+        }
+    } else {
+        // ===== epilogue (both CTAs): own 128 rows of the accumulator =====
+        const int q = warp & 3;
+        int acc = 0;
+        uint32_t aphase = 0;
+        int my_bad = 0;
+        int chunk_parity = 0;
+        for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+            const int m2 = tile % num_m2, n_blk = tile / num_m2;
+            const int row0 = m2 * 2 * BM + (int)rank * BM + q * 32;
+            const int row = row0 + lane;
+            const bool row_ok = row < args.op_rows;
+            const float sc = row_ok ? __ldg(args.inv_scale + row) : 0.0f;
+            mbar_wait(bar_tfull + 8 * acc, aphase);
+            tc_fence_after();
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                uint32_t v[32];
+                tc_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + acc * BN + c * 32, v);
+                tc_wait_ld();
+                if (c == BN / 32 - 1) {                            // accumulator drained: tell the leader
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(map_to_cta(bar_tempty + 8 * acc, 0));
+                }
+                const long long p0 = (long long)n_blk * BN + c * 32;
+                if (MODE == STORE_F64_PIXEL_MAJOR) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const long long p = p0 + j;
+                        if (row_ok && p < args.n_pixels)
+                            args.out_f64[p * args.op_rows + row] = (double)(__uint_as_float(v[j]) * sc);
+                    }
+                } else {
+                    int iv[32];
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float f = __uint_as_float(v[j]) * sc;
+                        my_bad |= !(fabsf(f) < 2147483648.0f);
+                        iv[j] = __float2int_rz(f);
+                    }
+                    if (MODE == STORE_TMA) {
+                        const uint32_t buf = epi_base + (q * 2 + chunk_parity) * EPI_BUF;
+                        if (lane == 0) tma_store_wait_read<1>();
+                        __syncwarp();
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const uint32_t dst = buf + lane * 128 + ((j ^ (lane & 7)) << 4);
+                            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "r"(iv[4 * j]),
+                                         "r"(iv[4 * j + 1]), "r"(iv[4 * j + 2]), "r"(iv[4 * j + 3])
+                                         : "memory");
+                        }
+                        fence_async_smem();
+                        __syncwarp();
+                        if (p0 < args.n_pixels && row0 < args.op_rows) {
+                            if (lane == 0) {
+                                tma_store_2d(&map_out, buf, (int)p0, row0);
+                                tma_store_commit();
+                            }
+                            chunk_parity ^= 1;
+                        }
+                    } else {
+                        int32_t *dst = args.table + (long long)row * args.image_stride + p0;
+                        if (row_ok && p0 + 32 <= args.n_pixels && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+                            // a lane owns one row: 32 consecutive pixels = one 128-byte line, as 8 streaming 16-byte stores
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                __stcs(reinterpret_cast<int4 *>(dst) + j,
+                                       make_int4(iv[4 * j], iv[4 * j + 1], iv[4 * j + 2], iv[4 * j + 3]));
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) {
+                                const long long p = p0 + j;
+                                if (row_ok && p < args.n_pixels) dst[j] = iv[j];
+                            }
+                        }
+                    }
+                }
+            }
+            acc ^= 1;
+            if (acc == 0) aphase ^= 1;
+        }
+        if (MODE == STORE_TMA && lane == 0) tma_store_wait_all();
+        if (MODE != STORE_F64_PIXEL_MAJOR && args.bad != nullptr && my_bad) atomicAdd(args.bad, 1);
+    }
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();                            // neither CTA frees TMEM while the other may still be written
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TMEM_COLS)
                      : "memory");
     }
 }
@@ -463,6 +730,9 @@ int gemm_launch(const uint16_t *d_packed, int n, long long n_pixels, const uint1
     int mode = STORE_F64_PIXEL_MAJOR;
     map_out = map_b;
     if (d_table != nullptr) {
+        // (register stores straight to global, one 128-byte line per lane, were measured instead of the
+        // swizzled staging + TMA store to relieve shared memory: 77 ms against 16 ms -- 32 lines per store
+        // instruction; they remain the path of unaligned tables only)
         const bool tma_ok = (image_stride % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_table) & 15) == 0);
         mode = tma_ok ? STORE_TMA : STORE_DIRECT;
         if (tma_ok && (rc = make_map_2d(&map_out, CU_TENSOR_MAP_DATA_TYPE_INT32, d_table, n_pixels, op_rows,
@@ -489,6 +759,34 @@ int gemm_launch(const uint16_t *d_packed, int n, long long n_pixels, const uint1
     RTI_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const long long tiles = (long long)args.num_m_blks * args.num_n_blks;
     RTI_REQUIRE(tiles < (1ll << 31), "rbf shared: too many tiles (%lld); split the pixel range", tiles);
+    // CTA pairs (cta_group::2) unless RTI_GEMM_2CTA=0
+    static const bool two_cta = !(getenv("RTI_GEMM_2CTA") && getenv("RTI_GEMM_2CTA")[0] == '0');
+    if (two_cta) {
+        const long long tiles2 = (long long)((args.num_m_blks + 1) / 2) * args.num_n_blks;
+        // persistent pairs with a static tile stride: launch exactly as many clusters as can be resident at once
+        // (a GPC with an odd number of usable SMs cannot pair its last one)
+#define RTI_GEMM2_LAUNCH(M)                                                                                      \
+    do {                                                                                                         \
+        RTI_CUDA(cudaFuncSetAttribute(rbf_shared_gemm2_kernel<M>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                      SMEM2_BYTES));                                                             \
+        cudaLaunchConfig_t cfg = {};                                                                             \
+        cfg.gridDim = dim3(sms / 2 * 2);                                                                         \
+        cfg.blockDim = dim3(THREADS);                                                                            \
+        cfg.dynamicSmemBytes = SMEM2_BYTES;                                                                      \
+        int max_clusters = 0;                                                                                    \
+        RTI_CUDA(cudaOccupancyMaxActiveClusters(&max_clusters, rbf_shared_gemm2_kernel<M>, &cfg));               \
+        if (max_clusters < 1) max_clusters = 1;                                                                  \
+        const int clusters = (int)(tiles2 < max_clusters ? tiles2 : max_clusters);                               \
+        rbf_shared_gemm2_kernel<M><<<2 * clusters, THREADS, SMEM2_BYTES, stream>>>(map_hi, map_lo, map_b, map_out, \
+                                                                                  args);                         \
+    } while (0)
+        if (mode == STORE_TMA) RTI_GEMM2_LAUNCH(STORE_TMA);
+        else if (mode == STORE_DIRECT) RTI_GEMM2_LAUNCH(STORE_DIRECT);
+        else RTI_GEMM2_LAUNCH(STORE_F64_PIXEL_MAJOR);
+#undef RTI_GEMM2_LAUNCH
+        RTI_LAUNCHED("rbf_shared_gemm2_kernel");
+        return RTI_OK;
+    }
     const int grid = (int)(tiles < sms ? tiles : sms);
 #define RTI_GEMM_LAUNCH(M)                                                                                       \
     do {                                                                                                         \

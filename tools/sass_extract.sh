@@ -13,12 +13,14 @@ OUT=profiles/${TAG}_sass_summary.txt
   echo "# columns: kernel, then count of each opcode family found in its SASS"
   echo "# UTCHMMA = tcgen05.mma (fp16/bf16 kinds), UTCBAR = tcgen05.commit, LDTM = tcgen05.ld (TMEM -> registers),"
   echo "# UTMALDG/UTMASTG = cp.async.bulk.tensor (TMA tile load/store), UBLKCP = cp.async.bulk (TMA 1-D),"
-  echo "# SYNCS = mbarrier, DMMA = fp64 tensor core mma.sync, LDGSTS = cp.async, MUFU = special function unit"
+  echo "# SYNCS = mbarrier, DMMA = fp64 tensor core mma.sync, LDGSTS = cp.async, MUFU = special function unit;"
+  echo "# 2CTA = instructions carrying the .2CTA modifier (cta_group::2: pair MMA, pair TMA load, multicast commit)"
   cuobjdump -sass "$SO" | awk '
     /Function :/ { fn=$3; order[++n]=fn; next }
     fn != "" {
       if (match($0, /(UTCHMMA|UTCQMMA|UTCIMMA|UTCBAR|UTCATOMSWS|LDTM|STTM|UTMALDG|UTMASTG|UTMAPF|UBLKCP|UBLKPF|SYNCS|DMMA|HMMA|LDGSTS|MUFU|DFMA|FFMA|STG|LDG|ATOMS|REDUX)[A-Z0-9_.]*/)) {
-        op=substr($0, RSTART, RLENGTH); sub(/\..*/, "", op); c[fn SUBSEP op]++; ops[op]=1
+        full=substr($0, RSTART, RLENGTH); op=full; sub(/\..*/, "", op); c[fn SUBSEP op]++; ops[op]=1
+        if (full ~ /2CTA/) { c[fn SUBSEP "2CTA"]++; ops["2CTA"]=1 }
       }
     }
     END {
