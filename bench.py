@@ -247,32 +247,34 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
     inten = torch.empty((px, N_LIGHTS), dtype=torch.int32, device="cuda")
     _capi.call("rti_gather_soa", d_frames.data_ptr(), p, d_cams.data_ptr(), N_LIGHTS, 0, rows_s, COLS,
                lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), S)
-    w = torch.empty((px, N_LIGHTS), dtype=torch.float64, device="cuda")
-    tiles = (rows_s // 16) * (COLS // 16)
-    nbytes = lib.rti_rbf_pcg_workspace_bytes(N_LIGHTS, tiles)
-    work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-    iters = torch.empty(px, dtype=torch.int32, device="cuda")
-    tab = torch.empty((G, G, px), dtype=torch.int32, device="cuda")
+    from rti_b200 import analysis
+    tab = torch.empty((G * G, px), dtype=torch.int32, device="cuda")
     max_iters, tol = 32, 0.01
+    state = {}
 
     def pcg():
-        bad.zero_()
-        _capi.call("rti_rbf_fit_pcg", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), rows_s, COLS, N_LIGHTS,
-                   w.data_ptr(), work.data_ptr(), nbytes, max_iters, tol, iters.data_ptr(), bad.data_ptr(), S)
+        # rti_rbf_fit_pcg + direct fp64 refit of the pixels it reports (not converged / weights too large for
+        # float32 distances), as the drop-in runs it
+        hbad = torch.zeros(1, dtype=torch.int32, device="cuda")
+        state["w"], state["info"] = analysis.rbf_fit_device_pcg(lx, ly, inten, rows_s, COLS, hbad, max_iters=max_iters,
+                                                              tol=tol)
+        state["singular"] = hbad
 
     fit_ms = best(pcg, reps=2)
-    singular_tiles, unconverged = (int(v) for v in bad.tolist())
+    w, info = state["w"], state["info"]
+    singular_tiles, unconverged = info["singular_tiles"], info["refit"]
     bad.zero_()
-    ev_ms = best(lambda: _capi.call("rti_rbf_table_fast", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), px, N_LIGHTS,
-                                    d_axis.data_ptr(), G, tab.data_ptr(), px, bad.data_ptr(), S), reps=2)
-    steps = iters.abs().float()
+    ev_ms = best(lambda: analysis.rbf_table_device(lx, ly, w, d_axis, G, tab, bad, fp64_idx=info["fp64_idx"]), reps=2)
+    tab = tab.view(G, G, px)
     # sampled oracle check (scipy's algorithm in fp64: solve(A, d), cdist(grid, nodes) @ w)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import rti_oracle as orc
     ax = orc.light_axis()
     rng = np.random.default_rng(5)
     worst, flips = 0.0, 0
-    sample_px = rng.integers(0, px, 8)
+    sample_px = [int(v) for v in rng.integers(0, px, 6)]
+    if info["fp64_idx"] is not None and info["fp64_idx"].numel():
+        sample_px += [int(v) for v in info["fp64_idx"][:2].tolist()]        # and two of the fp64-routed pixels
     for q in sample_px:
         q = int(q)
         l1, l2, dd = lx[q].cpu().numpy(), ly[q].cpu().numpy(), inten[q].cpu().numpy()
@@ -285,11 +287,13 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
     res["rbf_per_pixel_lights"] = {
         "sample": "%d pixels (%d ROI rows) x %d lights, fit + 100x100 table" % (px, rows_s, N_LIGHTS),
         "path": "tile-preconditioned CG fit (rti_rbf_fit_pcg: fp64 DMMA tile inverse, float32 distances + fp64 sums, "
-                "batched tcgen05 preconditioner) + float32-distance table (rti_rbf_table_fast)",
+                "batched tcgen05 preconditioner) + float32-distance table (rti_rbf_table_fast); the reported pixels "
+                "through rti_rbf_fit_soa + rti_rbf_table (fp64), inside the timed calls",
         "fit_ms": fit_ms, "table_ms": ev_ms, "value": px * N_LIGHTS / ((fit_ms + ev_ms) * 1e-3) / 1e6, "unit": UNIT,
         "fit_us_per_pixel": fit_ms * 1e3 / px, "table_us_per_pixel": ev_ms * 1e3 / px,
-        "cg_steps": {"mean": float(steps.mean().item()), "max": int(steps.max().item()), "limit": max_iters,
-                     "tol": tol, "unconverged": unconverged},
+        "cg_steps": {"mean": info["steps_mean"], "limit": max_iters, "tol": tol,
+                     "pixels_refitted_and_evaluated_in_fp64": unconverged,
+                     "why": "not converged, or |w|_2 > 10 tol / 1.2e-7 (float32 distances no longer hold the tolerance)"},
         "roofline": {"bound": "sfu", "kernel": "rbf_eval_f32_kernel",
                      "achieved": G * G * N_LIGHTS * px / (ev_ms * 1e-3) / 1e12, "peak": sm_peak / 1e12,
                      "unit": "Tsqrt/s", "frac": G * G * N_LIGHTS * px / (ev_ms * 1e-3) / sm_peak,
@@ -299,7 +303,7 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
         "parity_sample": {"pixels": int(len(sample_px)), "grid_max_rel": worst, "tolerance": 1e-3,
                           "table_entries_off_beyond_tolerance": flips},
         "singular_tiles": singular_tiles, "unrepresentable": int(bad[0].item())}
-    del work, tab, iters
+    del tab, state
     # ---- the same on the fp64 path (direct DMMA Cholesky + fp64 evaluation), rows [0, 2)
     px2 = 2 * COLS
     batch = 148 * 2
@@ -307,6 +311,7 @@ def secondary_rbf(torch, lib, _capi, d_frames, d_cams, d_axis, p):
     work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
     tab = torch.empty((G, G, px2), dtype=torch.int32, device="cuda")
     bad.zero_()
+    w = torch.empty((px2, N_LIGHTS), dtype=torch.float64, device="cuda")
     fit2 = best(lambda: _capi.call("rti_rbf_fit_soa", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), px2, N_LIGHTS,
                                    w.data_ptr(), work.data_ptr(), nbytes, batch, bad.data_ptr(), S))
     ev2 = best(lambda: _capi.call("rti_rbf_table", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), px2, N_LIGHTS,
@@ -570,18 +575,18 @@ def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
     inten = torch.empty((spx, N4), dtype=torch.int32, device="cuda")
     _capi.call("rti_gather_soa", frames.data_ptr(), P_loc, d_cams.data_ptr(), N4, r0, rs, R4,
                lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), S)
-    w = torch.empty((spx, N4), dtype=torch.float64, device="cuda")
-    tiles = ((rs + 15) // 16) * (R4 // 16)
-    nbytes = lib.rti_rbf_pcg_workspace_bytes(N4, tiles)
-    work = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
-    iters = torch.empty(spx, dtype=torch.int32, device="cuda")
-    tview = table.view(-1)[:G * G * spx]
-    fit_ms = timed(lambda: (sbad.zero_(), _capi.call(
-        "rti_rbf_fit_pcg", lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), rs, R4, N4, w.data_ptr(), work.data_ptr(),
-        nbytes, 48, 0.01, iters.data_ptr(), sbad.data_ptr(), S)))
-    unconv = int(sbad[1].item())
-    ev_ms = timed(lambda: _capi.call("rti_rbf_table_fast", lx.data_ptr(), ly.data_ptr(), w.data_ptr(), spx, N4,
-                                     d_axis.data_ptr(), G, tview.data_ptr(), spx, sbad.data_ptr(), S))
+    from rti_b200 import analysis
+    st4 = {}
+
+    def fit4():
+        hb = torch.zeros(1, dtype=torch.int32, device="cuda")
+        st4["w"], st4["info"] = analysis.rbf_fit_device_pcg(lx, ly, inten, rs, R4, hb, max_iters=48, tol=0.01)
+
+    tview = table.view(-1)[:G * G * spx].view(G * G, spx)
+    fit_ms = timed(fit4)
+    w, info4 = st4["w"], st4["info"]
+    unconv = info4["refit"]
+    ev_ms = timed(lambda: analysis.rbf_table_device(lx, ly, w, d_axis, G, tview, sbad, fp64_idx=info4["fp64_idx"]))
     # one sampled pixel per rank against scipy's algorithm in fp64
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import rti_oracle as orc
@@ -590,7 +595,7 @@ def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
     gref = orc.rbf_grid(l1, l2, orc.rbf_fit(l1, l2, dd), orc.light_axis())
     ggot = orc.rbf_grid(l1, l2, w[q].cpu().numpy(), orc.light_axis())
     rbf_rel = float(np.max(np.abs(ggot - gref)) / np.max(np.abs(gref)))
-    steps_mean = float(iters.abs().float().mean().item())
+    steps_mean = info4["steps_mean"]
     op_ms, shared_ms, fit_ms, ev_ms, rbf_rel, unconv_max = max_over_ranks([op_ms, shared_ms, fit_ms, ev_ms, rbf_rel, unconv])
     pp_s = (fit_ms + ev_ms) * (P_loc / spx) / 1e3
     n_pad, r_pad = -(-N4 // 64) * 64, -(-op_rows // 128) * 128
@@ -599,11 +604,12 @@ def config4_strong(torch, dist, _capi, lib, rank, world, hbm_peak):
                           "unit": UNIT, "executed_tflops_per_gpu": 4.0 * r_pad * n_pad * P_loc / (shared_ms * 1e-3) / 1e12,
                           "what": "pack + tcgen05 contraction into the int32 table, complete run of the rank's rows"},
         "per_pixel_lights": {"sample_pixels_per_rank": spx, "fit_ms": fit_ms, "table_ms": ev_ms,
-                             "cg_steps_mean": steps_mean, "unconverged": int(unconv_max),
+                             "cg_steps_mean": steps_mean, "pixels_in_fp64": int(unconv_max),
                              "extrapolated_full_roi_s": pp_s, "value": P * N4 / pp_s / 1e6, "unit": UNIT,
                              "grid_max_rel_vs_oracle": rbf_rel,
-                             "what": "pcg fit + float32-distance table on a 16-row sample per rank; sampled, extrapolated"}}
-    del lx, ly, inten, w, work, iters
+                             "what": "pcg fit + float32-distance table (fp64 kernels for the pixels the fit reports) on a "
+                                     "16-row sample per rank; sampled, extrapolated"}}
+    del lx, ly, inten, w
     out = {"workload": "synthetic 4096x4096 ROI x 1000 light samples, PTM fit + 100x100 light grid (BASELINE configs[3])",
            "scaling": "strong", "ranks": world, "rows_per_rank": nr, "sub_slab_rows": SUB,
            "ptm_ms": ptm_ms, "gather_ms": gather_ms, "total_ms": total_ms,

@@ -174,7 +174,9 @@ int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten
  * d_iters: optional int32 [rows*cols], steps each pixel took (negated for a pixel that did
  * not converge).  d_bad: int32[2]; [0] counts
  * tiles whose centre matrix is singular (duplicate nodes), [1] pixels that did not reach tol
- * within max_iters steps -- refit those with rti_rbf_fit_soa.  3 <= n <= 1025. */
+ * within max_iters steps OR whose weights are so large (|w|_2 > 10 tol / 1.2e-7: node pairs a few
+ * 1e-5 apart) that float32 distances no longer hold the tolerance -- refit those with
+ * rti_rbf_fit_soa and evaluate them with rti_rbf_table (fp64).  3 <= n <= 1025. */
 int64_t rti_rbf_pcg_workspace_bytes(int n, int64_t tiles);
 int rti_rbf_fit_pcg(const float *d_lx, const float *d_ly, const int32_t *d_inten,
                     int rows, int cols, int n, double *d_weights,

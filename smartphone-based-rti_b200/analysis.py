@@ -190,6 +190,7 @@ class InterpolationResult:
         self.stack = stack              # mode "ptm" from frame records: coefficients are fitted on demand, or by
         self._coef_done = coef is not None   # the fused fit + table kernel while the table is produced
         self.precision = precision      # "fast" | "fp64" (RBF modes)
+        self.fp64_idx = None            # "fast" RBF: pixel indices (device int64) that are evaluated in fp64 anyway
         self.path = path or mode        # which kernels produced / will produce the numbers
         self._d_axis = None
 
@@ -503,13 +504,19 @@ def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
             return res
     if precision == "fast" and 3 <= n <= 1025:
         weights, info = rbf_fit_device_pcg(lx, ly, inten, range_val, range_val, bad)
-        path = "rbf: pcg fit (%d of %d pixels refitted directly) + float32-distance table" % (info["refit"], n_pixels)
+        fp64_idx = info["fp64_idx"]
+        path = ("rbf: pcg fit + float32-distance table; %d of %d pixels (not converged, or weights too large for "
+                "float32 distances) fitted and evaluated in fp64" % (info["refit"], n_pixels))
     else:
         weights = rbf_fit_device(lx, ly, inten, bad)
-        path = "rbf: direct fp64 fit + %s table" % ("float32-distance" if precision == "fast" else "fp64")
+        fp64_idx = None
+        precision = "fp64"                 # (n outside the pcg kernel's range: everything on the fp64 kernels)
+        path = "rbf: direct fp64 fit + fp64 table"
     _raise_if_bad(bad, "RBF")
-    return InterpolationResult("rbf", range_val, range_val, axis, lx=lx, ly=ly, weights=weights,
-                               precision=precision, path=path)
+    res = InterpolationResult("rbf", range_val, range_val, axis, lx=lx, ly=ly, weights=weights,
+                              precision=precision, path=path)
+    res.fp64_idx = fp64_idx
+    return res
 
 
 def rbf_fit_device(lx, ly, inten, bad, out=None):
@@ -554,7 +561,7 @@ def rbf_fit_device_pcg(lx, ly, inten, rows, cols, bad, max_iters=None, tol=None)
                _stream_ptr(torch))
     del work
     singular_tiles, unconverged = (int(v) for v in pbad.tolist())
-    info = {"singular_tiles": singular_tiles, "refit": 0, "max_iters": max_iters, "tol": tol}
+    info = {"singular_tiles": singular_tiles, "refit": 0, "max_iters": max_iters, "tol": tol, "fp64_idx": None}
     if singular_tiles or unconverged:
         redo = iters <= 0 if singular_tiles == 0 else (iters <= 0) | ~torch.isfinite(weights).all(dim=1)
         if singular_tiles:
@@ -562,6 +569,7 @@ def rbf_fit_device_pcg(lx, ly, inten, rows, cols, bad, max_iters=None, tol=None)
             redo |= iters >= max_iters
         idx = redo.nonzero().view(-1)
         info["refit"] = int(idx.numel())
+        info["fp64_idx"] = idx             # these pixels are also EVALUATED in fp64 (table_tiles)
         if idx.numel():
             w_sub = rbf_fit_device(lx[idx].contiguous(), ly[idx].contiguous(), inten[idx].contiguous(), bad)
             weights[idx] = w_sub
@@ -603,11 +611,30 @@ def _table_rows(res: InterpolationResult, r0, tr, out, bad):
             raise ValueError("shared-light tables are produced in one piece")
         res.shared.table(out, tp, bad[1:])
     else:
-        n = res.weights.shape[1]
-        fn = "rti_rbf_table_fast" if res.precision == "fast" else "rti_rbf_table"
-        _capi.call(fn, res.lx.data_ptr() + 4 * p0 * n, res.ly.data_ptr() + 4 * p0 * n,
-                   res.weights.data_ptr() + 8 * p0 * n, tp, n, res.d_axis().data_ptr(), g, out.data_ptr(), tp,
-                   bad.data_ptr() + 4, S)
+        rbf_table_device(res.lx, res.ly, res.weights, res.d_axis(), g, out, bad[1:], p0=p0, count=tp,
+                         precision=res.precision, fp64_idx=res.fp64_idx)
+
+
+def rbf_table_device(lx, ly, weights, d_axis, g, out, bad, p0=0, count=None, precision="fast", fp64_idx=None):
+    """int32 table columns of pixels [p0, p0 + count) of a per-pixel linear-RBF model into out (g*g, count):
+    float32-distance kernel for precision "fast", except the pixels listed in fp64_idx (weights too large for
+    float32 distances, see rbf_fit_device_pcg), which are evaluated by the fp64 kernel and scattered in."""
+    torch = _torch()
+    S = _stream_ptr(torch)
+    n = weights.shape[1]
+    count = lx.shape[0] - p0 if count is None else count
+    fn = "rti_rbf_table_fast" if precision == "fast" else "rti_rbf_table"
+    _capi.call(fn, lx.data_ptr() + 4 * p0 * n, ly.data_ptr() + 4 * p0 * n, weights.data_ptr() + 8 * p0 * n, count, n,
+               d_axis.data_ptr(), g, out.data_ptr(), count, bad.data_ptr(), S)
+    if precision == "fast" and fp64_idx is not None and fp64_idx.numel():
+        sel = fp64_idx[(fp64_idx >= p0) & (fp64_idx < p0 + count)]
+        k = int(sel.numel())
+        if k:
+            sub = torch.empty((g * g, k), dtype=torch.int32, device="cuda")
+            lx_s, ly_s, w_s = lx[sel].contiguous(), ly[sel].contiguous(), weights[sel].contiguous()
+            _capi.call("rti_rbf_table", lx_s.data_ptr(), ly_s.data_ptr(), w_s.data_ptr(), k, n, d_axis.data_ptr(), g,
+                       sub.data_ptr(), k, bad.data_ptr(), S)
+            out[:, sel - p0] = sub
 
 
 def _raise_if_bad_table(bad):
