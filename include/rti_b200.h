@@ -188,10 +188,13 @@ int rti_rbf_table(const float *d_lx, const float *d_ly, const double *d_weights,
                   int64_t n_pixels, int n, const double *d_axis, int g,
                   int32_t *d_table, int64_t image_stride, int32_t *d_bad, rti_stream_t stream);
 /* The same table with the node distances formed in float32 (one MUFU.SQRT per term) and the
- * products with the fp64 weights and the running sums kept in fp64: grid values within ~1e-5 of
- * the largest value against scipy's fp64 evaluation (north_star allows 1e-3), so an int32
- * entry can differ from the reference's, by one, only where the fp64 value lies that close to
- * an integer.  Bound by the SFU (G*G*n square roots per pixel), ~2x the fp64 form. */
+ * products with the fp64 weights and the running sums kept in fp64.  Absolute error of a grid
+ * value ~ 1.2e-7 * |w|_2 (each distance carries a float32 rounding): ~5e-5 of the largest value
+ * for typical pixels (north_star allows 1e-3), but over budget for pixels with node pairs ~1e-5
+ * apart, whose weights reach 1e6 -- rti_rbf_fit_pcg reports those pixels, evaluate them with
+ * rti_rbf_table.  An int32 entry can differ from the reference's, by one, only where the fp64
+ * value lies that close to an integer.  Bound by the SFU (G*G*n square roots per pixel),
+ * ~1.7x the fp64 form. */
 int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const double *d_weights,
                        int64_t n_pixels, int n, const double *d_axis, int g,
                        int32_t *d_table, int64_t image_stride, int32_t *d_bad, rti_stream_t stream);
