@@ -556,6 +556,51 @@ def test_full_size_properties(torch_cuda):
         assert torch.equal(frame.view(-1).to(torch.int32), table[v, u].clamp(0, 255))   # (c)
 
 
+def test_fused_kernel_whole_slab_against_independent_least_squares(torch_cuda):
+    """Every pixel of a 32 x 1024 slab at the bench's light count (N = 500), not a sample: the fused
+    gather + fit + table kernel (rti_ptm_fit_table_frames, the headline kernel, two frame chunks per tile)
+    against an independent fp64 solution of the same least-squares problems -- the oracle's light vectors
+    and design matrix (analysis.py:228-232, 282-290), solved by torch's batched QR on the GPU instead of the
+    kernel's normal equations -- and the table against the polynomial of those coefficients
+    (analysis.py:303-315, 404-407), every one of the 32768 x 10^4 entries."""
+    from rti_b200 import _capi, synthetic
+    torch = torch_cuda
+    rows, cols, n, row0 = 32, 1024, 500, 700
+    rng = np.random.default_rng(31)
+    cams = synthetic.camera_positions(1024, cols, n, rng)
+    frames = rng.integers(0, 256, (n, rows, cols), dtype=np.uint8)
+    p = rows * cols
+    ax = orc.light_axis()
+    d_f, d_c, d_ax = dev(torch, frames), dev(torch, cams), dev(torch, ax)
+    coef = torch.empty((6, p), dtype=torch.float64, device="cuda")
+    table = torch.empty((100, 100, p), dtype=torch.int32, device="cuda")
+    bad = torch.zeros(2, dtype=torch.int32, device="cuda")
+    _capi.call("rti_ptm_fit_table_frames", d_f.data_ptr(), p, d_c.data_ptr(), n, row0, rows, cols, d_ax.data_ptr(), 100,
+               coef.data_ptr(), p, table.data_ptr(), p, bad.data_ptr(), None)
+    torch.cuda.synchronize()
+    assert bad.sum().item() == 0
+    worst_coef, off = 0.0, 0
+    gu = torch.from_numpy(ax).cuda()
+    lu = gu[None, None, :]
+    lv = gu[None, :, None]
+    for y in range(rows):
+        lx, ly, inten = orc.gather_soa(frames[:, y:y + 1], cams, row0=row0 + y)      # (1, cols, n)
+        design = torch.from_numpy(np.stack([orc.ptm_design(lx[0, x], ly[0, x]) for x in range(0, cols, 1)])).cuda()
+        rhs = torch.from_numpy(inten[0].astype(np.float64)).cuda()[:, :, None]
+        sol = torch.linalg.lstsq(design, rhs, driver="gels").solution[:, :, 0]       # (cols, 6)
+        got = coef[:, y * cols:(y + 1) * cols].T
+        worst_coef = max(worst_coef, ((got - sol).abs().amax(dim=1) / sol.abs().amax(dim=1)).max().item())
+        a = got                                                                       # the kernel's own coefficients
+        val = (a[:, 0, None, None] * lu * lu + a[:, 1, None, None] * lv * lv + a[:, 2, None, None] * lu * lv
+               + a[:, 3, None, None] * lu + a[:, 4, None, None] * lv + a[:, 5, None, None])   # (cols, 100 v, 100 u)
+        t = table[:, :, y * cols:(y + 1) * cols].permute(2, 0, 1)
+        diff = t != torch.trunc(val).to(torch.int32)
+        # a differently grouped fp64 sum may cross an integer only when the value sits on it
+        off += int((diff & ((val - torch.round(val)).abs() > 1e-9)).sum().item())
+    assert worst_coef < PTM_COEF_RTOL, worst_coef
+    assert off == 0
+
+
 # ------------------------------------------------------------------------------ linear RBF
 RBF_GRID_RTOL = 1e-8        # achieved (fp64 Cholesky of the reduced SPD system); north_star allows 1e-3
 
