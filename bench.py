@@ -189,8 +189,19 @@ def cpu_reference(pixels_per_core, steps=1, warmup=0, mode="ptm", cores=None):
     who = "the unmodified reference functions (baseline/_ref)" if kind else "oracle port of"
     sample = ("%d random pixels x %d lights per step (%d per core), %s %s; extrapolates linearly in pixels"
               % (pixels, N_LIGHTS, pixels_per_core, who, what))
-    return {"value": value, "unit": UNIT, "cores": cores, "kind": "reference" if kind else "port",
-            "sample": sample}, dt * 1e3
+    out = {"value": value, "unit": UNIT, "cores": cores, "kind": "reference" if kind else "port", "sample": sample}
+    if not kind:
+        # the port against the UNMODIFIED reference functions, measured where the reference is mounted (the build
+        # container, one core; tools/time_reference_cpu.py): how much slower the reference as written is
+        try:
+            with open(os.path.join(ROOT, "profiles", "r02_reference_vs_port_cpu.json")) as f:
+                r = json.load(f)[mode]
+            out["port_over_unmodified_reference"] = {
+                "ratio": r["port_over_reference"], "where": "build container, 1 core, N=%d" % N_LIGHTS,
+                "reference_ms_per_pixel": r["reference_ms_per_pixel"], "port_ms_per_pixel": r["port_ms_per_pixel"]}
+        except Exception:
+            pass
+    return out, dt * 1e3
 
 
 def run_reference(args, rank):
