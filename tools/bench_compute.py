@@ -115,7 +115,15 @@ def main():
                 for y in (0, r // 2, r - 1):                        # three ROI rows of four images, re-evaluated
                     gr = res.grids(y * r, r)                        # (r, 100, 100) fp64
                     for v, u in ((0, 0), (3, 7), (50, 50), (99, 99)):
-                        ok = ok and bool(np.array_equal(mapped[v][u][y], np.trunc(gr[:, v, u]).astype(np.int32)))
+                        want = np.trunc(gr[:, v, u]).astype(np.int32)
+                        if ptm:
+                            ok = ok and bool(np.array_equal(mapped[v][u][y], want))
+                        else:
+                            # the default linear-RBF path is float32-distance (north_star: 1e-3): an entry may differ
+                            # by one where the fp64 value lies within that tolerance of an integer
+                            d = mapped[v][u][y] != want
+                            near = np.abs(gr[:, v, u] - np.rint(gr[:, v, u])) <= 1e-3 * np.abs(gr).max()
+                            ok = ok and bool(np.all(np.abs(mapped[v][u][y] - want) <= 1) and np.all(near[d]))
                 out[mode] = {"total_s": total, "stages_s": st.times, "result_bytes": size, "mapped_load_s": map_s,
                              "result_file_ok": bool(ok), "path": res.path,
                              "mpixel_lights_per_s_wall": r * r * n / total / 1e6}
