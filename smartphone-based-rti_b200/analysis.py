@@ -39,6 +39,11 @@ _cst = _default_constants           # rebound by install() to the reference's co
 RBF_PRECISION = os.environ.get("RTI_RBF_PRECISION", "fast")
 RBF_PCG_MAX_ITERS = 32
 RBF_PCG_TOL = 0.01                  # max-norm node residual, in intensity units
+# Linear RBF from frame records: when the three (P, N) arrays of compute_intensities plus the (P, N) weights would
+# take more than this fraction of the free device memory (20 B per pixel.light: 21 GB at 1024^2 x 1000, 335 GB at
+# 4096^2 x 1000), nothing is materialised for the whole ROI: gather, fit and evaluation run per band of ROI rows
+# while the table is produced (same numbers; the weights of a pixel are recomputed if res[y][x] asks for them).
+RBF_BANDED_FRACTION = 0.25
 # Device bytes of one table tile buffer (two are used): prepare_images_data / write_table_file evaluate
 # the [ly][lx] images in ROW TILES of the ROI through these, so the (G, G, P) table never has to fit on
 # the device (42 GB at 1024^2, 671 GB at 4096^2).
@@ -191,6 +196,7 @@ class InterpolationResult:
         self._coef_done = coef is not None   # the fused fit + table kernel while the table is produced
         self.precision = precision      # "fast" | "fp64" (RBF modes)
         self.fp64_idx = None            # "fast" RBF: pixel indices (device int64) that are evaluated in fp64 anyway
+        self._band = None               # banded RBF (stack-backed, no whole-ROI arrays): the last fitted band
         self.path = path or mode        # which kernels produced / will produce the numbers
         self._d_axis = None
 
@@ -220,11 +226,57 @@ class InterpolationResult:
             raise IndexError("list index out of range")
         return _ResultRow(self, y % self.rows)
 
+    @property
+    def banded(self):
+        return self.mode == "rbf" and self.weights is None and self.stack is not None
+
+    def rbf_band(self, r0, tr):
+        """(lx, ly, weights, fp64_idx) of ROI rows [r0, r0 + tr) of a banded RBF result: gather + fit of just
+        those rows (rti_gather_soa on the frame rows, then the pcg or the direct fit); the last band is kept."""
+        if self._band is not None and self._band[0] == (r0, tr):
+            return self._band[1]
+        torch = _torch()
+        st = self.stack
+        tp = tr * st.cols
+        shape = (tp, st.n)
+        lx = torch.empty(shape, dtype=torch.float32, device="cuda")
+        ly = torch.empty(shape, dtype=torch.float32, device="cuda")
+        inten = torch.empty(shape, dtype=torch.int32, device="cuda")
+        _capi.call("rti_gather_soa", st.d_frames.data_ptr() + r0 * st.cols, st.n_pixels, st.d_cams.data_ptr(), st.n,
+                   st.row0 + r0, tr, st.cols, lx.data_ptr(), ly.data_ptr(), inten.data_ptr(), _stream_ptr(torch))
+        bad = torch.zeros(1, dtype=torch.int32, device="cuda")
+        if self.precision == "fast" and 3 <= st.n <= 1025:
+            weights, info = rbf_fit_device_pcg(lx, ly, inten, tr, st.cols, bad)
+            idx = info["fp64_idx"]
+        else:
+            weights, idx = rbf_fit_device(lx, ly, inten, bad), None
+        _raise_if_bad(bad, "RBF")
+        del inten
+        self._band = ((r0, tr), (lx, ly, weights, idx))
+        return self._band[1]
+
     def grids(self, p0, count):
         """float64 (count, G, G) grids of pixels [p0, p0 + count)."""
         torch = _torch()
         g = self.axis.size
         out = torch.empty((count, g, g), dtype=torch.float64, device="cuda")
+        if self.banded:
+            # the 16-row band(s) that hold the pixels (tile-aligned, so the fit is the one the table gets)
+            done = 0
+            while done < count:
+                p = p0 + done
+                y = p // self.cols
+                b0 = (y // 16) * 16
+                tr = min(16, self.rows - b0)
+                lx, ly, w, _ = self.rbf_band(b0, tr)
+                q0 = p - b0 * self.cols
+                c = min(count - done, tr * self.cols - q0)
+                n = w.shape[1]
+                _capi.call("rti_rbf_grids", lx.data_ptr() + 4 * q0 * n, ly.data_ptr() + 4 * q0 * n,
+                           w.data_ptr() + 8 * q0 * n, c, n, self.d_axis().data_ptr(), g,
+                           out.data_ptr() + 8 * done * g * g, _stream_ptr(torch))
+                done += c
+            return out.cpu().numpy()
         if self.mode == "ptm":
             _capi.call("rti_ptm_grids", self.coef.data_ptr() + 8 * p0, self.n_pixels, count,
                        self.d_axis().data_ptr(), g, out.data_ptr(), _stream_ptr(torch))
@@ -482,6 +534,17 @@ def interpolate_intensities(data, interpolate_PTM=False, first_only=False):
         return InterpolationResult("ptm", range_val, range_val, axis, row0=stack.row0, stack=stack,
                                    path="ptm: fused gather+fit+table per row tile (rti_ptm_fit_table_frames)")
 
+    from_records = (all(isinstance(a, DeviceArrayView) for a in data) and data[0]._soa is data[1]._soa is data[2]._soa
+                    and data[0].shape[:2] == (range_val, range_val))
+    if not interpolate_PTM and from_records and data[0]._soa._arrays is None:
+        stack = data[0]._soa.stack
+        free, _total = torch.cuda.mem_get_info()
+        if 20.0 * stack.n_pixels * stack.n > RBF_BANDED_FRACTION * free:
+            precision = RBF_PRECISION if RBF_PRECISION in ("fast", "fp64") else "fast"
+            return InterpolationResult("rbf", range_val, range_val, axis, row0=stack.row0, stack=stack,
+                                       precision=precision,
+                                       path="rbf: banded (gather + %s fit + table per band of ROI rows; nothing "
+                                            "materialised for the whole ROI)" % ("pcg" if precision == "fast" else "direct"))
     lx, ly, inten = _as_device_soa(data, range_val)
     n_pixels, n = lx.shape
     bad = torch.zeros(1, dtype=torch.int32, device="cuda")
@@ -610,6 +673,9 @@ def _table_rows(res: InterpolationResult, r0, tr, out, bad):
         if (r0, tr) != (0, res.rows):
             raise ValueError("shared-light tables are produced in one piece")
         res.shared.table(out, tp, bad[1:])
+    elif res.banded:
+        lx, ly, w, idx = res.rbf_band(r0, tr)
+        rbf_table_device(lx, ly, w, res.d_axis(), g, out, bad[1:], precision=res.precision, fp64_idx=idx)
     else:
         rbf_table_device(res.lx, res.ly, res.weights, res.d_axis(), g, out, bad[1:], p0=p0, count=tp,
                          precision=res.precision, fp64_idx=res.fp64_idx)
@@ -671,6 +737,13 @@ def table_tiles(res: InterpolationResult, tile_bytes=None):
     tr_max = int(max(1, min(res.rows, tile_bytes // max(1, gg * 4 * res.cols))))
     if res.mode == "rbf_shared":
         tr_max = res.rows
+    if res.banded:
+        # whole 16-row pixel tiles per band (the pcg fit's tiles), bounded by the SoA / weights / workspace memory
+        free, _total = torch.cuda.mem_get_info()
+        per_row = res.cols * res.stack.n * 64                      # SoA + weights + pcg state, bytes per ROI row
+        tr_mem = int(max(16, (free // 4) // max(per_row, 1)))
+        tr_max = max(16, (min(tr_max, tr_mem) // 16) * 16)
+        tr_max = min(tr_max, res.rows)
     # whole 16-byte granules per tile keep the fused kernel's frame rows aligned (its fast path)
     while tr_max < res.rows and (tr_max * res.cols) % 16 != 0:
         tr_max += 1

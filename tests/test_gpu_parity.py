@@ -800,6 +800,33 @@ def test_rbf_call_surface(torch_cuda, ref_small, monkeypatch, precision):
         rti_b200.interpolate_intensities((lx, ly, inten))
 
 
+@pytest.mark.parametrize("precision", ["fast", "fp64"])
+def test_rbf_banded_route_equals_whole_roi_route(torch_cuda, monkeypatch, precision):
+    """Large ROIs in linear-RBF mode never materialise the (R, R, N) arrays or the weights: gather, fit and
+    evaluation run per band of ROI rows while the table is produced (analysis.RBF_BANDED_FRACTION).  Forced on
+    here for a 40 x 40 ROI with 3 bands and small table tiles: same table and same res[y][x] as the eager route."""
+    import rti_b200
+    from rti_b200 import analysis, synthetic
+    r, n = 40, 30
+    frames, cams = synthetic.lambertian_stack(r, r, n, seed=17, rows_total=1024, row0=100)
+    monkeypatch.setattr(rti_b200.constants, "ROI_DIAMETER", r)
+    monkeypatch.setattr(analysis, "RBF_PRECISION", precision)
+    monkeypatch.setattr(analysis, "TABLE_TILE_BYTES", 16 * r * 100 * 100 * 4)          # 16 ROI rows per table tile
+    recs = synthetic.as_records(frames, cams)
+    eager = rti_b200.interpolate_intensities(rti_b200.compute_intensities(recs))
+    assert not eager.banded
+    t_eager = np.array(rti_b200.prepare_images_data(eager))
+    monkeypatch.setattr(analysis, "RBF_BANDED_FRACTION", 0.0)
+    banded = rti_b200.interpolate_intensities(rti_b200.compute_intensities(recs))
+    assert banded.banded and banded.path.startswith("rbf: banded")
+    t_banded = np.array(rti_b200.prepare_images_data(banded))
+    assert np.array_equal(t_eager, t_banded)
+    for y, x in [(0, 0), (15, 39), (16, 0), (39, 39), (33, 7)]:
+        assert np.array_equal(eager[y][x], banded[y][x])
+    g = banded.grids(15 * r + 30, 25)                                  # a pixel range that crosses a band boundary
+    assert np.array_equal(g, eager.grids(15 * r + 30, 25))
+
+
 @pytest.mark.parametrize("ptm", [True, False])
 def test_compute_tiles_table_under_device_memory_cap(torch_cuda, monkeypatch, tmp_path, ptm):
     """compute() evaluates the table in row tiles through a bounded device buffer and
