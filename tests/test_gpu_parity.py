@@ -846,8 +846,14 @@ def test_compute_tiles_table_under_device_memory_cap(torch_cuda, monkeypatch, tm
     monkeypatch.chdir(tmp_path)
     (tmp_path / "assets").mkdir()
     total = torch.cuda.get_device_properties(0).total_memory
+    # the cap counts what the caching allocator has RESERVED: drop what earlier tests left (tensors kept alive for
+    # asynchronous calls can pin a large segment) and allow 256 MB beyond whatever remains
+    import gc
+    torch.cuda.synchronize()
+    del _KEEPALIVE[:]
+    gc.collect()
     torch.cuda.empty_cache()
-    torch.cuda.set_per_process_memory_fraction(min(1.0, (256 << 20) / total))
+    torch.cuda.set_per_process_memory_fraction(min(1.0, (torch.cuda.memory_reserved() + (256 << 20)) / total))
     try:
         rti_b200.compute("cap", from_storage=True, storage_filepath=path, interpolate_PTM=ptm)
     finally:
