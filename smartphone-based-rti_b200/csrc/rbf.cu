@@ -467,7 +467,7 @@ rbf_eval_kernel(const float *__restrict__ lx, const float *__restrict__ ly, cons
 // done with two shifts and an add on the integer pipe (exponent re-bias 127 -> 1023) because
 // F2F.F64.F32 shares the XU pipe with MUFU, which is the unit this kernel is bound by:
 // G*G*N square roots per pixel at 16 per clock per SM.
-// A CTA owns PB consecutive pixels; a thread owns FE_U consecutive directions of one grid row.
+// A CTA owns PB consecutive pixels; a thread owns a small patch of the light grid (below).
 // --------------------------------------------------------------------------------------
 constexpr int FE_KCH = 128;             // nodes staged per chunk
 
@@ -476,27 +476,34 @@ __device__ __forceinline__ double widen_pos_f32(float r) {
     return __hiloint2double((int)((b >> 3) + 0x38000000u), (int)(b << 29));   // r = 0 maps to 2^-127
 }
 
-template <int PB, int FE_U>
+// A thread owns a patch of FE_V consecutive grid rows x FE_U consecutive columns for PB pixels, so dx is shared by
+// the rows and dy^2 by the columns of its patch: one node costs 2 LDS + FE_U + 2 FE_V float instructions and
+// FE_U * FE_V terms of 5 instructions each (FFMA, MUFU.SQRT, LEA.HI, IMAD.SHL, DFMA).
+template <int PB, int FE_U, int FE_V>
 __global__ void __launch_bounds__(EV_THREADS)
 rbf_eval_f32_kernel(const float *__restrict__ lx, const float *__restrict__ ly, const double *__restrict__ weights,
-                    int64_t n_pixels, int n, const double *__restrict__ axis, int g, int strips_per_row,
-                    int32_t *__restrict__ out, int64_t image_stride, int32_t *__restrict__ bad) {
+                          int64_t n_pixels, int n, const double *__restrict__ axis, int g, int strips_per_row,
+                          int row_groups, int32_t *__restrict__ out, int64_t image_stride, int32_t *__restrict__ bad) {
     __shared__ float2 s_xy[PB][FE_KCH];
     __shared__ double s_w[PB][FE_KCH];
     const int64_t p0 = (int64_t)blockIdx.x * PB;
-    const int strip = blockIdx.y * EV_THREADS + threadIdx.x;
-    const bool live = strip < strips_per_row * g;
-    const int v = live ? strip / strips_per_row : 0;
-    const int u0 = live ? (strip - v * strips_per_row) * FE_U : 0;
-    float gx[FE_U];
+    const int patch = blockIdx.y * EV_THREADS + threadIdx.x;
+    const bool live = patch < strips_per_row * row_groups;
+    const int vg = live ? patch / strips_per_row : 0;
+    const int v0 = vg * FE_V;
+    const int u0 = live ? (patch - vg * strips_per_row) * FE_U : 0;
+    float gx[FE_U], gy[FE_V];
 #pragma unroll
     for (int j = 0; j < FE_U; ++j) gx[j] = (float)axis[min(u0 + j, g - 1)];
-    const float gy = (float)axis[v];
-    double acc[PB][FE_U];
+#pragma unroll
+    for (int i = 0; i < FE_V; ++i) gy[i] = (float)axis[min(v0 + i, g - 1)];
+    double acc[PB][FE_V][FE_U];
 #pragma unroll
     for (int q = 0; q < PB; ++q)
 #pragma unroll
-        for (int j = 0; j < FE_U; ++j) acc[q][j] = 0.0;
+        for (int i = 0; i < FE_V; ++i)
+#pragma unroll
+            for (int j = 0; j < FE_U; ++j) acc[q][i][j] = 0.0;
 
     for (int k0 = 0; k0 < n; k0 += FE_KCH) {
         const int kc = min(FE_KCH, n - k0);
@@ -514,42 +521,53 @@ rbf_eval_f32_kernel(const float *__restrict__ lx, const float *__restrict__ ly, 
             for (int k = 0; k < kc; ++k) {
                 const float2 xy = s_xy[q][k];
                 const double wk = s_w[q][k];
-                const float dy = gy - xy.y;
-                const float dy2 = dy * dy;
+                float dx[FE_U], dy2[FE_V];
 #pragma unroll
-                for (int j = 0; j < FE_U; ++j) {
-                    const float dx = gx[j] - xy.x;
-                    float r;
-                    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(dx, dx, dy2)));
-                    acc[q][j] = fma(widen_pos_f32(r), wk, acc[q][j]);
+                for (int j = 0; j < FE_U; ++j) dx[j] = gx[j] - xy.x;
+#pragma unroll
+                for (int i = 0; i < FE_V; ++i) {
+                    const float dy = gy[i] - xy.y;
+                    dy2[i] = dy * dy;
                 }
+#pragma unroll
+                for (int i = 0; i < FE_V; ++i)
+#pragma unroll
+                    for (int j = 0; j < FE_U; ++j) {
+                        float r;
+                        asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(fmaf(dx[j], dx[j], dy2[i])));
+                        acc[q][i][j] = fma(widen_pos_f32(r), wk, acc[q][i][j]);
+                    }
             }
         }
     }
     if (!live) return;
     bool any_bad = false;
 #pragma unroll
-    for (int j = 0; j < FE_U; ++j) {
-        if (u0 + j >= g) break;
-        const int64_t d = (int64_t)v * g + u0 + j;
-        int32_t *dst = out + d * image_stride + p0;
-        if (PB % 4 == 0 && p0 + PB <= n_pixels && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+    for (int i = 0; i < FE_V; ++i) {
+        if (v0 + i >= g) break;
 #pragma unroll
-            for (int q = 0; q < PB; q += 4) {
-                int val[4];
+        for (int j = 0; j < FE_U; ++j) {
+            if (u0 + j >= g) break;
+            const int64_t d = (int64_t)(v0 + i) * g + u0 + j;
+            int32_t *dst = out + d * image_stride + p0;
+            if (PB % 4 == 0 && p0 + PB <= n_pixels && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    if (!(fabs(acc[q + i][j]) < 2147483648.0)) any_bad = true;
-                    val[i] = trunc_i32(acc[q + i][j]);
+                for (int q = 0; q < PB; q += 4) {
+                    int val[4];
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        if (!(fabs(acc[q + e][i][j]) < 2147483648.0)) any_bad = true;
+                        val[e] = trunc_i32(acc[q + e][i][j]);
+                    }
+                    __stcs(reinterpret_cast<int4 *>(dst + q), make_int4(val[0], val[1], val[2], val[3]));
                 }
-                __stcs(reinterpret_cast<int4 *>(dst + q), make_int4(val[0], val[1], val[2], val[3]));
-            }
-        } else {
+            } else {
 #pragma unroll
-            for (int q = 0; q < PB; ++q) {
-                if (p0 + q < n_pixels) {
-                    if (!(fabs(acc[q][j]) < 2147483648.0)) any_bad = true;
-                    dst[q] = trunc_i32(acc[q][j]);
+                for (int q = 0; q < PB; ++q) {
+                    if (p0 + q < n_pixels) {
+                        if (!(fabs(acc[q][i][j]) < 2147483648.0)) any_bad = true;
+                        dst[q] = trunc_i32(acc[q][i][j]);
+                    }
                 }
             }
         }
@@ -630,16 +648,16 @@ extern "C" int rti_rbf_grids(const float *d_lx, const float *d_ly, const double 
                                   "rti_rbf_grids");
 }
 
-template <int PB, int U>
+template <int PB, int U, int V>
 static int rbf_fast_launch(const float *d_lx, const float *d_ly, const double *d_weights, int64_t n_pixels, int n,
-                           const double *d_axis, int g, int32_t *d_table, int64_t image_stride, int32_t *d_bad,
-                           rti_stream_t stream, const char *who) {
-    const int strips_per_row = (g + U - 1) / U;
-    const unsigned gy = (unsigned)(((int64_t)strips_per_row * g + EV_THREADS - 1) / EV_THREADS);
+                                 const double *d_axis, int g, int32_t *d_table, int64_t image_stride, int32_t *d_bad,
+                                 rti_stream_t stream, const char *who) {
+    const int strips_per_row = (g + U - 1) / U, row_groups = (g + V - 1) / V;
+    const unsigned gy = (unsigned)(((int64_t)strips_per_row * row_groups + EV_THREADS - 1) / EV_THREADS);
     const int64_t bx = (n_pixels + PB - 1) / PB;
     RTI_REQUIRE(bx <= 0x7fffffffLL, "%s: too many pixels", who);
-    rbf_eval_f32_kernel<PB, U><<<dim3((unsigned)bx, gy), EV_THREADS, 0, as_stream(stream)>>>(
-        d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, strips_per_row, d_table, image_stride, d_bad);
+    rbf_eval_f32_kernel<PB, U, V><<<dim3((unsigned)bx, gy), EV_THREADS, 0, as_stream(stream)>>>(
+        d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, strips_per_row, row_groups, d_table, image_stride, d_bad);
     RTI_LAUNCHED("rbf_eval_f32_kernel");
     return RTI_OK;
 }
@@ -653,15 +671,15 @@ extern "C" int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const do
     RTI_REQUIRE(image_stride >= n_pixels, "%s: image_stride < pixels", who);
 #define RTI_FAST_ARGS d_lx, d_ly, d_weights, n_pixels, n, d_axis, g, d_table, image_stride, d_bad, stream, who
     static const int variant = getenv("RTI_RBF_FAST_VARIANT") ? atoi(getenv("RTI_RBF_FAST_VARIANT")) : 0;
-    // development A/B (tools/prof_rbf.py, N = 500, 4736 pixels): <8,4> 6.94 ms, <4,10> 7.14, <8,5> 6.84,
-    // <2,10> 6.62, <4,4> 6.55 ms = 0.78 of the SFU peak (ncu: XU pipe 80 %, issue slots 76 %, stalls = MIO
-    // throttle, i.e. the MUFU queue is full); 0 is the shipped shape.  Also measured and dropped: MUFU.RSQ + FMUL
-    // instead of MUFU.SQRT 7.30 ms (one more issue slot per term); register caps for 4 / 5 CTAs per SM
-    // (64 / 48 registers) 7.13 / 7.47 ms; <2,8> at 64 registers 7.89 ms; <4,8> 7.66 ms
+    // development A/B (tools/prof_rbf.py, N = 500, 4736 pixels; <pixels, columns, rows> per thread):
+    // <4,4,2> 6.19 ms = 0.82 of the SFU peak, <4,2,4> 6.19, <4,5,2> 6.36, <2,4,2> 6.52, <4,4,1> 6.55 (ncu of that
+    // shape: XU pipe 80 %, issue slots 76 %, stall = MIO throttle, i.e. the MUFU queue is full), <4,3,2> 6.69,
+    // <8,2,2> 6.95, <2,4,4> 7.66, <4,4,3> 8.33; 1-row strips <8,4> 6.94, <4,10> 7.14, <2,10> 6.62.  Also measured and
+    // dropped: MUFU.RSQ + FMUL instead of MUFU.SQRT 7.30 ms; register caps for 4 / 5 CTAs per SM 7.13 / 7.47 ms
     switch (variant) {
-    case 1: return rbf_fast_launch<8, 4>(RTI_FAST_ARGS);
-    case 2: return rbf_fast_launch<2, 10>(RTI_FAST_ARGS);
-    default: return rbf_fast_launch<4, 4>(RTI_FAST_ARGS);
+    case 1: return rbf_fast_launch<4, 4, 1>(RTI_FAST_ARGS);
+    case 2: return rbf_fast_launch<4, 2, 4>(RTI_FAST_ARGS);
+    default: return rbf_fast_launch<4, 4, 2>(RTI_FAST_ARGS);
     }
 #undef RTI_FAST_ARGS
 }
