@@ -194,7 +194,7 @@ int rti_rbf_table(const float *d_lx, const float *d_ly, const double *d_weights,
  * apart, whose weights reach 1e6 -- rti_rbf_fit_pcg reports those pixels, evaluate them with
  * rti_rbf_table.  An int32 entry can differ from the reference's, by one, only where the fp64
  * value lies that close to an integer.  Bound by the SFU (G*G*n square roots per pixel),
- * ~1.7x the fp64 form. */
+ * ~1.8x the fp64 form. */
 int rti_rbf_table_fast(const float *d_lx, const float *d_ly, const double *d_weights,
                        int64_t n_pixels, int n, const double *d_axis, int g,
                        int32_t *d_table, int64_t image_stride, int32_t *d_bad, rti_stream_t stream);
