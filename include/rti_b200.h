@@ -162,6 +162,21 @@ int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32_t *d_inten
                     int64_t n_pixels, int n, double *d_weights,
                     void *d_work, int64_t work_bytes, int batch,
                     int32_t *d_bad, rti_stream_t stream);
+/* rti_rbf_fit_soa without the caller-provided workspace.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid allocation).  The Cholesky workspace is
+ * a file-scope device array of RTI_RBF_STATIC_SCRATCH_BYTES inside the library, held by every GPU
+ * that loads it until the process exits; the call allocates nothing (no cudaMalloc / cudaFree / pool).
+ * Same kernel, inputs, outputs and error codes as rti_rbf_fit_soa (d_bad may be NULL); pixels in
+ * flight = min(296, scratch / rti_rbf_workspace_bytes(n, 1)).  n whose one-pixel workspace exceeds
+ * the scratch (n > 1983) is rejected with RTI_ERR_ARG.  All calls share the scratch: calls that
+ * overlap on the GPU (two streams, two host threads on one device) race -- serialise them.  Nothing
+ * in the scratch must start at zero; the previous call's contents are overwritten.  The first call on
+ * a device looks the array's device address up (cudaGetSymbolAddress): make it outside graph capture. */
+#define RTI_RBF_STATIC_SCRATCH_BYTES (32ll << 20)
+int rti_rbf_fit_soa_static(const float *d_lx, const float *d_ly, const int32_t *d_inten,
+                           int64_t n_pixels, int n, double *d_weights,
+                           int32_t *d_bad, rti_stream_t stream);
 /* The same fit, tile-preconditioned (rbf_pcg.cu): the SoA arrays describe a rows x cols slab
  * (pixel = y*cols + x).  Per 16x16 pixel tile the reduced matrix of the tile-centre pixel is
  * inverted once in fp64 and serves as the preconditioner of conjugate-gradient solves of every

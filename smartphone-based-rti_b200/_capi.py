@@ -61,6 +61,7 @@ SIGNATURES = {
     "rti_grids_to_table": (_i, [_p, _l, _i, _p, _l, _p, _p]),
     "rti_rbf_workspace_bytes": (_l, [_i, _i]),
     "rti_rbf_fit_soa": (_i, [_p, _p, _p, _l, _i, _p, _p, _l, _i, _p, _p]),
+    "rti_rbf_fit_soa_static": (_i, [_p, _p, _p, _l, _i, _p, _p, _p]),
     "rti_rbf_pcg_workspace_bytes": (_l, [_i, _l]),
     "rti_rbf_fit_pcg": (_i, [_p, _p, _p, _i, _i, _i, _p, _p, _l, _i, _d, _p, _p, _p]),
     "rti_rbf_table": (_i, [_p, _p, _p, _l, _i, _p, _i, _p, _l, _p, _p]),

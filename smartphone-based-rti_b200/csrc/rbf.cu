@@ -16,6 +16,7 @@
 // is one contiguous cp.async stream into shared memory.  The two right-hand sides ride
 // along as two extra rows of the matrix, which performs the forward substitution inside
 // the factorisation; only the backward substitution remains.
+#include <mutex>
 #include "rbf_tiles.cuh"
 
 namespace rti {
@@ -608,6 +609,60 @@ extern "C" int rti_rbf_fit_soa(const float *d_lx, const float *d_ly, const int32
     const int64_t stride = rti_rbf_workspace_bytes(n, 1) / (int64_t)sizeof(double);
     rbf_fit_kernel<<<(unsigned)grid, RBF_THREADS, smem, as_stream(stream)>>>(
         d_lx, d_ly, d_inten, n_pixels, n, d_weights, reinterpret_cast<double *>(d_work), stride, d_bad);
+    RTI_LAUNCHED("rbf_fit_kernel");
+    return RTI_OK;
+}
+
+// ---- the same fit for callers that may not allocate (no counterpart in the reference) ----------
+// The L workspace lives in a file-scope device array instead of a caller-provided buffer: every
+// GPU that loads the library holds RTI_RBF_STATIC_SCRATCH_BYTES until the process exits.  In host
+// code the array's name is only a stand-in for the symbol, so its device address is looked up once
+// per device (with that device current) and cached.  All calls share the array: calls that overlap
+// on the GPU (different streams, or different host threads) race on it.  Nothing in it has to start
+// at zero -- rbf_fit_kernel writes every L block and D^-T tile before it reads them, which is also
+// what lets rti_rbf_fit_soa run on uninitialised workspaces -- so the contents the previous call
+// left behind are simply overwritten.
+constexpr int64_t RBF_STATIC_SCRATCH_BYTES = 32ll << 20;
+static __device__ __align__(256) double g_rbf_static_scratch[RBF_STATIC_SCRATCH_BYTES / sizeof(double)];
+static double *g_rbf_static_ptr[64] = {};
+static std::mutex g_rbf_static_mutex;
+
+extern "C" int rti_rbf_fit_soa_static(const float *d_lx, const float *d_ly, const int32_t *d_inten,
+                                      int64_t n_pixels, int n, double *d_weights, int32_t *d_bad,
+                                      rti_stream_t stream) {
+    RTI_REQUIRE(d_lx && d_ly && d_inten && d_weights, "rti_rbf_fit_soa_static: NULL pointer");
+    RTI_REQUIRE(n_pixels > 0, "rti_rbf_fit_soa_static: empty input");
+    RTI_REQUIRE(n >= 2, "rti_rbf_fit_soa_static: need >= 2 nodes, got %d", n);
+    const int64_t per_pixel = rti_rbf_workspace_bytes(n, 1);
+    RTI_REQUIRE(per_pixel <= RBF_STATIC_SCRATCH_BYTES,
+                "rti_rbf_fit_soa_static: n = %d needs %lld bytes of scratch per pixel, the built-in scratch holds "
+                "%lld (n <= 1983); use rti_rbf_fit_soa with a caller-provided workspace", n, (long long)per_pixel,
+                (long long)RBF_STATIC_SCRATCH_BYTES);
+    const size_t smem = rbf_fit_smem(n);
+    RTI_REQUIRE(4 * rbf_mpad(n) <= 4 * STG + TS * LDS && smem <= 227 * 1024,
+                "rti_rbf_fit_soa_static: n = %d exceeds what the kernel's shared memory holds", n);
+    int dev = 0;
+    RTI_CUDA(cudaGetDevice(&dev));
+    RTI_REQUIRE(dev >= 0 && dev < 64, "rti_rbf_fit_soa_static: device ordinal %d out of range", dev);
+    double *scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_rbf_static_mutex);
+        if (g_rbf_static_ptr[dev] == nullptr) {
+            void *p = nullptr;
+            RTI_CUDA(cudaGetSymbolAddress(&p, g_rbf_static_scratch));
+            RTI_REQUIRE(p != nullptr, "rti_rbf_fit_soa_static: the scratch symbol has no address on device %d", dev);
+            g_rbf_static_ptr[dev] = static_cast<double *>(p);
+        }
+        scratch = g_rbf_static_ptr[dev];
+    }
+    // pixels in flight: what the scratch holds, at most two CTAs per SM of a 148-SM part
+    int64_t batch = RBF_STATIC_SCRATCH_BYTES / per_pixel;
+    if (batch > 2 * 148) batch = 2 * 148;
+    RTI_CUDA(cudaFuncSetAttribute(rbf_fit_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t grid = n_pixels < batch ? n_pixels : batch;
+    const int64_t stride = per_pixel / (int64_t)sizeof(double);
+    rbf_fit_kernel<<<(unsigned)grid, RBF_THREADS, smem, as_stream(stream)>>>(
+        d_lx, d_ly, d_inten, n_pixels, n, d_weights, scratch, stride, d_bad);
     RTI_LAUNCHED("rbf_fit_kernel");
     return RTI_OK;
 }
