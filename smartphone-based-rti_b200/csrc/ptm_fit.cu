@@ -187,26 +187,44 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
     const int64_t p0 = (int64_t)blockIdx.x * SOA_PIX;
     const void *base[3] = {lx, ly, inten};
 
+    // VEC16 addressing, hoisted out of the stage loop: thread t always fetches chunk position c = t & 7 of
+    // rows j*16 + (t >> 3), j = 0..7, of all three arrays.  16-byte chunks are aligned in MEMORY, not in
+    // the light index: a row starts at element p*n, a multiple of 4 only when n is, so the chunk holding
+    // the row start may begin with up to 3 elements of the previous row (the consumer masks them).
+    // Per row: the address of this thread's chunk in stage 0 (per array) and the number of elements from
+    // there to the row's end (<= 0: nothing to fetch, also for rows past n_pixels).  A stage then costs
+    // one 64-bit add per copy; a copy with nothing to fetch has src-size 0 (zero fill, no access).
+    const int vc = t & 7, vr = t >> 3;
+    const char *v_src[3][8];
+    int v_len[8];
+    if (VEC16) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int64_t p = p0 + j * 16 + vr;
+            const int64_t e0 = p * n;
+            const int lead_j = (int)(e0 & 3);
+            const bool in = p < n_pixels;
+            v_len[j] = in ? n + lead_j - 4 * vc : 0;
+            const int64_t first = in ? e0 - lead_j + 4 * vc : 0;
+#pragma unroll
+            for (int a = 0; a < 3; ++a) v_src[a][j] = reinterpret_cast<const char *>(base[a]) + first * 4;
+        }
+    }
+    const unsigned v_dst = (unsigned)__cvta_generic_to_shared(s_soa) + vr * 128 + ((vc ^ (vr & 7)) << 4);
+
     auto issue = [&](int stage, int i0) {
         unsigned char *dst0 = s_soa + stage * SOA_STAGE_BYTES;
         if (VEC16) {
 #pragma unroll
-            for (int it = 0; it < 3 * SOA_PIX * 8 / SOA_PIX; ++it) {
-                const int idx = it * SOA_PIX + t;
-                const int a = it / 8;                              // 1024 chunks per array, 128 per `it`
-                const int rem = idx - a * (SOA_PIX * 8);
-                const int row = rem >> 3, c = rem & 7;
-                const int64_t p = p0 + row;
-                // 16-byte chunks are aligned in MEMORY, not in the light index: a row starts at element
-                // p*n, which is a multiple of 4 only when n is.  The chunk holding the row start may
-                // begin with up to 3 elements of the previous row; the consumer masks them.
-                const int64_t e0 = p * n;
-                const int64_t start = (e0 & ~(int64_t)3) + i0 + 4 * c;
-                int64_t nb = (p < n_pixels) ? (e0 + n - start) * 4 : 0;
-                nb = nb < 0 ? 0 : (nb > 16 ? 16 : nb);
-                const char *src = reinterpret_cast<const char *>(base[a]);
-                if (nb > 0) src += start * 4;
-                cp_async_zfill(dst0 + a * SOA_ARRAY_BYTES + row * 128 + ((c ^ (row & 7)) << 4), src, 16, (int)nb);
+            for (int j = 0; j < 8; ++j) {
+                const int left = v_len[j] - i0;                      // elements of the row from this chunk on
+                const int nb = 4 * (left < 0 ? 0 : (left > 4 ? 4 : left));
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const unsigned d = v_dst + stage * SOA_STAGE_BYTES + a * SOA_ARRAY_BYTES + j * 2048;
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d),
+                                 "l"(v_src[a][j] + (unsigned)i0 * 4u), "r"(nb));
+                }
             }
         } else {
             for (int it = 0; it < 3 * SOA_KL; ++it) {
