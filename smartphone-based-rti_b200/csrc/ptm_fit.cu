@@ -150,20 +150,29 @@ ptm_fit_frames_kernel(const uint8_t *__restrict__ frames, int64_t frame_stride,
 // --------------------------------------------------------------------------------------
 // Fit from materialised (lx, ly, intensity) arrays [pixel][n], light index fastest
 // (the compute_intensities layout, analysis.py:217-219).
-// A CTA owns 128 consecutive pixels, one per thread.  The three arrays are streamed through
-// shared memory in stages of 32 lights with cp.async (16-byte chunks: 8 consecutive threads
-// fetch one pixel's 128-byte line, so global reads are whole lines), double buffered.  Chunk
-// c of row t lives at chunk position c ^ (t & 7): the cp.async writes and the per-thread
-// LDS.128 reads (row = thread) are both bank-conflict free.  Every thread then owns its
-// pixel's 26 running sums: no cross-lane reduction, and the 6x6 solves run on all lanes.
+// A CTA owns 128 consecutive pixels and runs 256 threads: thread (half, pixel) accumulates lights
+// [16 half, 16 half + 16) of every stage of its pixel, the upper half hands its 26 sums to the lower one
+// through shared memory at the end (16 warps per SM instead of 8: with 2 warps per scheduler the fp64
+// and conversion latencies were exposed, issue slots 49 % busy; 0.381 -> 0.355 ms at 262 144 px x 500).
+// The three arrays are streamed through shared memory in stages of 32 lights with cp.async (16-byte
+// chunks: 8 consecutive threads fetch one pixel's 128-byte line, so global reads are whole lines),
+// double buffered; the source addresses are computed once per thread (12 pointers), a stage costs one
+// 64-bit add per copy (the per-copy 64-bit multiplies it replaces were 10 of ~50 issue slots per sample:
+// 0.408 -> 0.381 ms).  Chunk c of row t lives at chunk position c ^ (t & 7): the cp.async writes and
+// the per-thread LDS.128 reads (row = pixel) are both bank-conflict free.  Every pixel's 26 running
+// sums stay in registers: no cross-lane reduction, and the 6x6 solves run on all lanes of the lower half.
 // Lights past n and pixels past n_pixels are zero-filled by cp.async (src-size 0), which
 // adds exact zeros to the sums.  The 16-byte chunks are aligned in memory for ANY n: when
 // n % 4 != 0 a row's first chunk starts with 1-3 elements of the previous row, which the
 // owning thread zeroes after the load.
-// Bound: 12 B of HBM per pixel.light against 32 fp64 issue slots + 6 conversions; at full
-// fp64 rate that is ~7 TB/s, i.e. the kernel sits at the HBM / fp64 ridge.
+// Bound: 12 B of HBM per pixel.light against 26 fp64 instructions + 6 conversions; tools/peak_pipes.cu
+// (profiles/r02_peak_pipes.jsonl) measures 2.17 clocks per DFMA and scheduler, and a conversion that
+// involves fp64 costs ~2.8 clocks of the fp64 pipe on top of ~8.5 of the XU pipe: ~73 fp64-pipe clocks
+// per warp and sample = 0.31 ms at this size.  The kernel runs at 0.355 ms = 0.69 of the HBM rate
+// (0.73 at 1 M pixels); integer-pipe replacements of the conversions were measured slower (0.450 ms).
 // --------------------------------------------------------------------------------------
-constexpr int SOA_PIX = 128;                 // pixels per CTA = threads per CTA
+constexpr int SOA_PIX = 128;                 // pixels per CTA
+constexpr int SOA_THREADS = 256;             // two threads per pixel, each takes half of a stage's lights
 constexpr int SOA_KL = 32;                   // lights per stage (one 128-byte line per array and pixel)
 constexpr int SOA_ARRAY_BYTES = SOA_PIX * SOA_KL * 4;            // 16 KB
 constexpr int SOA_STAGE_BYTES = 3 * SOA_ARRAY_BYTES;             // 48 KB
@@ -178,29 +187,32 @@ __device__ __forceinline__ void cp_async_zfill(void *smem, const void *gmem, int
 }
 
 template <bool VEC16>
-__global__ void __launch_bounds__(SOA_PIX, 2)
+__global__ void __launch_bounds__(SOA_THREADS, 2)
 ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
                    const int32_t *__restrict__ inten, int64_t n_pixels, int n,
                    double *__restrict__ coef, int64_t plane_stride, int32_t *__restrict__ bad) {
     extern __shared__ __align__(16) unsigned char s_soa[];
     const int t = threadIdx.x;
+    const int tp = t & (SOA_PIX - 1);            // the thread's pixel (row of the stage)
+    const int half = t >> 7;                     // which 16 of a stage's 32 lights it accumulates
     const int64_t p0 = (int64_t)blockIdx.x * SOA_PIX;
     const void *base[3] = {lx, ly, inten};
 
     // VEC16 addressing, hoisted out of the stage loop: thread t always fetches chunk position c = t & 7 of
-    // rows j*16 + (t >> 3), j = 0..7, of all three arrays.  16-byte chunks are aligned in MEMORY, not in
+    // rows j*32 + (t >> 3), j = 0..3, of all three arrays.  16-byte chunks are aligned in MEMORY, not in
     // the light index: a row starts at element p*n, a multiple of 4 only when n is, so the chunk holding
     // the row start may begin with up to 3 elements of the previous row (the consumer masks them).
     // Per row: the address of this thread's chunk in stage 0 (per array) and the number of elements from
     // there to the row's end (<= 0: nothing to fetch, also for rows past n_pixels).  A stage then costs
     // one 64-bit add per copy; a copy with nothing to fetch has src-size 0 (zero fill, no access).
+    constexpr int VJ = SOA_PIX * 8 / SOA_THREADS;                    // rows per thread and array
     const int vc = t & 7, vr = t >> 3;
-    const char *v_src[3][8];
-    int v_len[8];
+    const char *v_src[3][VJ];
+    int v_len[VJ];
     if (VEC16) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const int64_t p = p0 + j * 16 + vr;
+        for (int j = 0; j < VJ; ++j) {
+            const int64_t p = p0 + j * (SOA_THREADS / 8) + vr;
             const int64_t e0 = p * n;
             const int lead_j = (int)(e0 & 3);
             const bool in = p < n_pixels;
@@ -216,20 +228,20 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
         unsigned char *dst0 = s_soa + stage * SOA_STAGE_BYTES;
         if (VEC16) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < VJ; ++j) {
                 const int left = v_len[j] - i0;                      // elements of the row from this chunk on
                 const int nb = 4 * (left < 0 ? 0 : (left > 4 ? 4 : left));
 #pragma unroll
                 for (int a = 0; a < 3; ++a) {
-                    const unsigned d = v_dst + stage * SOA_STAGE_BYTES + a * SOA_ARRAY_BYTES + j * 2048;
+                    const unsigned d = v_dst + stage * SOA_STAGE_BYTES + a * SOA_ARRAY_BYTES + j * (SOA_THREADS / 8) * 128;
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d),
                                  "l"(v_src[a][j] + (unsigned)i0 * 4u), "r"(nb));
                 }
             }
         } else {
-            for (int it = 0; it < 3 * SOA_KL; ++it) {
-                const int idx = it * SOA_PIX + t;
-                const int a = it / SOA_KL;
+            for (int it = 0; it < 3 * SOA_PIX * SOA_KL / SOA_THREADS; ++it) {
+                const int idx = it * SOA_THREADS + t;
+                const int a = idx / (SOA_PIX * SOA_KL);
                 const int rem = idx - a * (SOA_PIX * SOA_KL);
                 const int row = rem >> 5, w = rem & 31;
                 const int64_t p = p0 + row;
@@ -248,7 +260,7 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
     ne.clear();
     // VEC16 with n % 4 != 0: rows are misaligned by up to 3 elements, one more stage may be needed
     const int n_stages = (n + ((VEC16 && (n & 3)) ? 3 : 0) + SOA_KL - 1) / SOA_KL;
-    const int lead = VEC16 ? (int)(((p0 + t) * n) & 3) : 0;         // elements of the previous row in chunk 0
+    const int lead = VEC16 ? (int)(((p0 + tp) * n) & 3) : 0;        // elements of the previous row in chunk 0
     issue(0, 0);
     for (int s = 0; s < n_stages; ++s) {
         if (s + 1 < n_stages) {
@@ -258,10 +270,11 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
             asm volatile("cp.async.wait_group 0;\n" ::);
         }
         __syncthreads();
-        const unsigned char *row = s_soa + (s & 1) * SOA_STAGE_BYTES + t * 128;
+        const unsigned char *row = s_soa + (s & 1) * SOA_STAGE_BYTES + tp * 128;
 #pragma unroll 2
-        for (int c = 0; c < 8; ++c) {
-            const int off = (c ^ (t & 7)) << 4;
+        for (int cc = 0; cc < 4; ++cc) {
+            const int c = 4 * half + cc;
+            const int off = (c ^ (tp & 7)) << 4;
             float4 u = *reinterpret_cast<const float4 *>(row + off);
             float4 v = *reinterpret_cast<const float4 *>(row + SOA_ARRAY_BYTES + off);
             int4 w = *reinterpret_cast<const int4 *>(row + 2 * SOA_ARRAY_BYTES + off);
@@ -277,7 +290,25 @@ ptm_fit_soa_kernel(const float *__restrict__ lx, const float *__restrict__ ly,
         }
         __syncthreads();                     // buffer s & 1 is refilled by the next iteration's issue
     }
-    const int64_t p = p0 + t;
+    // the upper half hands its 26 sums over through shared memory ([sum][pixel], conflict free)
+    double *s_sum = reinterpret_cast<double *>(s_soa);
+    if (half == 1) {
+#pragma unroll
+        for (int k = 0; k < 15; ++k) s_sum[k * SOA_PIX + tp] = ne.g[k];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) s_sum[(15 + k) * SOA_PIX + tp] = ne.s[k];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) s_sum[(20 + k) * SOA_PIX + tp] = ne.r[k];
+    }
+    __syncthreads();
+    if (half == 1) return;
+#pragma unroll
+    for (int k = 0; k < 15; ++k) ne.g[k] += s_sum[k * SOA_PIX + tp];
+#pragma unroll
+    for (int k = 0; k < 5; ++k) ne.s[k] += s_sum[(15 + k) * SOA_PIX + tp];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) ne.r[k] += s_sum[(20 + k) * SOA_PIX + tp];
+    const int64_t p = p0 + tp;
     double a[6];
     const bool ok = solve_normal_eq(ne, (double)n, a);
     if (p < n_pixels) {
@@ -430,10 +461,10 @@ extern "C" int rti_ptm_fit_soa(const float *d_lx, const float *d_ly, const int32
     RTI_CUDA(cudaFuncSetAttribute(ptm_fit_soa_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOA_SMEM));
     RTI_CUDA(cudaFuncSetAttribute(ptm_fit_soa_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SOA_SMEM));
     if (vec16)
-        ptm_fit_soa_kernel<true><<<(unsigned)blocks, SOA_PIX, SOA_SMEM, as_stream(stream)>>>(
+        ptm_fit_soa_kernel<true><<<(unsigned)blocks, SOA_THREADS, SOA_SMEM, as_stream(stream)>>>(
             d_lx, d_ly, d_inten, n_pixels, n, d_coef, plane_stride, d_bad);
     else
-        ptm_fit_soa_kernel<false><<<(unsigned)blocks, SOA_PIX, SOA_SMEM, as_stream(stream)>>>(
+        ptm_fit_soa_kernel<false><<<(unsigned)blocks, SOA_THREADS, SOA_SMEM, as_stream(stream)>>>(
             d_lx, d_ly, d_inten, n_pixels, n, d_coef, plane_stride, d_bad);
     RTI_LAUNCHED("ptm_fit_soa_kernel");
     return RTI_OK;
