@@ -117,6 +117,50 @@ constexpr int RELIGHT_THREADS = 256;
 
 __device__ __forceinline__ int clamp_u8(int v) { return min(max(v, 0), 255); }   // interactive_relighting.py:35-36
 
+// HSV -> BGR of up to 4 consecutive pixels p0 .. p0 + cnt - 1 (p0 % 4 == 0) whose V channel is replaced
+// by val[] (interactive_relighting.py:37-38).  The 12 bytes of a full quad are 4-byte aligned in both byte
+// streams whenever their base pointers are: three word loads and three word stores instead of 8 + 12
+// byte accesses; the row position (for cvtColor's row tail, see hsv_row_tail) is derived once per quad.
+__device__ __forceinline__ void relight_bgr4(const uint8_t *__restrict__ hsv, uint8_t *__restrict__ out, int64_t p0,
+                                             int cnt, const int (&val)[4], int row_width) {
+    const bool words = cnt == 4 && (((reinterpret_cast<uintptr_t>(hsv) | reinterpret_cast<uintptr_t>(out)) & 3) == 0);
+    uint32_t w[3] = {0u, 0u, 0u};
+    if (words) {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(hsv + p0 * 3);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) w[i] = __ldcs(src + i);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 12; ++i)
+            if (i < 3 * cnt) w[i >> 2] |= (uint32_t)hsv[p0 * 3 + i] << (8 * (i & 3));
+    }
+    int x = 0, tail_from = 0;
+    if (row_width > 0) {
+        x = (int)(p0 % row_width);
+        tail_from = row_width - (row_width & 31);
+    }
+    uint32_t o[3] = {0u, 0u, 0u};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const int h8 = (w[(3 * q) >> 2] >> (8 * ((3 * q) & 3))) & 255;
+        const int s8 = (w[(3 * q + 1) >> 2] >> (8 * ((3 * q + 1) & 3))) & 255;
+        uint8_t c[3];
+        hsv2bgr_u8(h8, s8, val[q], row_width > 0 && x >= tail_from, c[0], c[1], c[2]);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) o[(3 * q + k) >> 2] |= (uint32_t)c[k] << (8 * ((3 * q + k) & 3));
+        if (++x == row_width) x = 0;
+    }
+    if (words) {
+        uint32_t *dst = reinterpret_cast<uint32_t *>(out + p0 * 3);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) dst[i] = o[i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < 12; ++i)
+            if (i < 3 * cnt) out[p0 * 3 + i] = (uint8_t)(o[i >> 2] >> (8 * (i & 3)));
+    }
+}
+
 template <typename T, bool HSV>
 __global__ void __launch_bounds__(RELIGHT_THREADS)
 relight_kernel(const T *__restrict__ coef, int64_t plane_stride, int64_t n_pixels, int row_width, T lu, T lv,
@@ -168,13 +212,7 @@ relight_kernel(const T *__restrict__ coef, int64_t plane_stride, int64_t n_pixel
             for (int q = 0; q < 4 && p0 + q < n_pixels; ++q) out[p0 + q] = (uint8_t)val[q];
         }
     } else {
-        for (int q = 0; q < 4 && p0 + q < n_pixels; ++q) {
-            const uint8_t *px = hsv + (p0 + q) * 3;
-            uint8_t b, g, r;
-            hsv2bgr_u8(px[0], px[1], val[q], hsv_row_tail(p0 + q, row_width), b, g, r);
-            uint8_t *o = out + (p0 + q) * 3;
-            o[0] = b; o[1] = g; o[2] = r;
-        }
+        relight_bgr4(hsv, out, p0, (int)min((int64_t)4, n_pixels - p0), val, row_width);
     }
 }
 
@@ -182,15 +220,29 @@ template <bool HSV>
 __global__ void __launch_bounds__(RELIGHT_THREADS)
 relight_image_kernel(const int32_t *__restrict__ image, int64_t n_pixels, int row_width,
                      const uint8_t *__restrict__ hsv, uint8_t *__restrict__ out) {
-    const int64_t p = (int64_t)blockIdx.x * RELIGHT_THREADS + threadIdx.x;
-    if (p >= n_pixels) return;
-    const int v = clamp_u8(__ldcs(image + p));
-    if (!HSV) {
-        out[p] = (uint8_t)v;
+    const int64_t p0 = ((int64_t)blockIdx.x * RELIGHT_THREADS + threadIdx.x) * 4;
+    if (p0 >= n_pixels) return;
+    const int cnt = (int)min((int64_t)4, n_pixels - p0);
+    int val[4] = {0, 0, 0, 0};
+    if (cnt == 4 && (reinterpret_cast<uintptr_t>(image) & 15) == 0) {
+        const int4 v = __ldcs(reinterpret_cast<const int4 *>(image + p0));
+        val[0] = clamp_u8(v.x); val[1] = clamp_u8(v.y); val[2] = clamp_u8(v.z); val[3] = clamp_u8(v.w);
     } else {
-        uint8_t b, g, r;
-        hsv2bgr_u8(hsv[p * 3], hsv[p * 3 + 1], v, hsv_row_tail(p, row_width), b, g, r);
-        out[p * 3] = b; out[p * 3 + 1] = g; out[p * 3 + 2] = r;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (q < cnt) val[q] = clamp_u8(__ldcs(image + p0 + q));
+    }
+    if (!HSV) {
+        if (cnt == 4 && (reinterpret_cast<uintptr_t>(out) & 3) == 0) {
+            *reinterpret_cast<uint32_t *>(out + p0) = (uint32_t)val[0] | ((uint32_t)val[1] << 8) |
+                                                      ((uint32_t)val[2] << 16) | ((uint32_t)val[3] << 24);
+        } else {
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (q < cnt) out[p0 + q] = (uint8_t)val[q];
+        }
+    } else {
+        relight_bgr4(hsv, out, p0, cnt, val, row_width);
     }
 }
 
@@ -321,7 +373,7 @@ extern "C" int rti_coef_to_f32(const double *d_coef, int64_t n_values, float *d_
 extern "C" int rti_relight_from_image(const int32_t *d_image, int64_t n_pixels, int row_width,
                                       const uint8_t *d_hsv, uint8_t *d_out, rti_stream_t stream) {
     RTI_REQUIRE(d_image && d_out && n_pixels > 0 && row_width >= 0, "rti_relight_from_image: bad arguments");
-    const int64_t blocks = (n_pixels + RELIGHT_THREADS - 1) / RELIGHT_THREADS;
+    const int64_t blocks = (n_pixels + RELIGHT_THREADS * 4 - 1) / (RELIGHT_THREADS * 4);
     if (d_hsv)
         relight_image_kernel<true><<<(unsigned)blocks, RELIGHT_THREADS, 0, as_stream(stream)>>>(
             d_image, n_pixels, row_width, d_hsv, d_out);

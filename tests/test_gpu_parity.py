@@ -377,6 +377,28 @@ def test_hsv2bgr_device_row_tail_matches_cv2_golden(torch_cuda, relight_rows_gol
             assert np.array_equal(img.cpu().numpy(), bgr), (key, prec)
 
 
+def test_relight_byte_streams_at_odd_addresses(torch_cuda, relight_rows_golden):
+    """The HSV / BGR byte streams are read and written as words when both are 4-byte aligned; any other
+    address (a view into a larger buffer) takes the byte path and gives the same image."""
+    from rti_b200 import _capi
+    torch = torch_cuda
+    g = relight_rows_golden
+    for key, off in (("hsv_5x399", 1), ("hsv_12x400", 2), ("hsv_9x37", 3)):
+        hsv, bgr = g[key], g["bgr_" + key[4:]]
+        rows, cols = hsv.shape[:2]
+        n = rows * cols
+        d_img = dev(torch, hsv[:, :, 2].astype(np.int32).reshape(-1))
+        d_hsv = torch.zeros(3 * n + 8, dtype=torch.uint8, device="cuda")
+        d_hsv[off:off + 3 * n] = torch.from_numpy(hsv.reshape(-1)).cuda()
+        d_out = torch.zeros(3 * n + 8, dtype=torch.uint8, device="cuda")
+        _capi.call("rti_relight_from_image", d_img.data_ptr(), n, cols, d_hsv.data_ptr() + off,
+                   d_out.data_ptr() + off, None)
+        torch.cuda.synchronize()
+        out = d_out.cpu().numpy()
+        assert np.array_equal(out[off:off + 3 * n].reshape(rows, cols, 3), bgr), key
+        assert not out[:off].any() and not out[off + 3 * n:].any()       # nothing written outside
+
+
 def test_relight_f32_map_within_one(torch_cuda):
     from rti_b200 import relighting
     torch = torch_cuda
