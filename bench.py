@@ -778,9 +778,15 @@ def run_gpu(args, rank, local_rank, world):
                 t = torch.tensor([dt], dtype=torch.float64, device="cuda")
                 dist.all_reduce(t, op=dist.ReduceOp.MAX)
                 dt = float(t.item())
+            # bytes that crossed PCIe in the last call: the table's 4 B per entry, or 2 B when the library moved
+            # it as int16 and widened it on the host (rti_b200.h: narrow transfer; same int32 table either way)
+            d2h_bytes = int(lib.rti_host_d2h_bytes())
             e2e = {"value": units_per_rank * world / dt / 1e6, "unit": UNIT,
                    "h2d_bytes_per_step": int(frames.nbytes + cams.nbytes + axis.nbytes),
-                   "d2h_bytes_per_step": int(table_bytes), "ms_per_step": dt * 1e3, "steps": args.e2e_steps,
+                   "d2h_bytes_per_step": d2h_bytes, "ms_per_step": dt * 1e3, "steps": args.e2e_steps,
+                   "table_bytes_delivered_per_step": int(table_bytes),
+                   "transfer": "int16 over PCIe, widened to int32 by host threads" if d2h_bytes < table_bytes
+                   else "int32 over PCIe",
                    "api": "rti_ptm_compute_host (pinned host frames -> int32 table in pinned host memory)"}
             lib.rti_destroy()
             # the host table of the last e2e step against the oracle (the host call numbers rows from 0)
@@ -810,7 +816,11 @@ def run_gpu(args, rank, local_rank, world):
                                "pinned buffer, %d rank(s) concurrently" % world,
                                "bare_copy_ms": bare * 1e3, "bare_copy_gbs_per_rank": table_bytes / bare / 1e9,
                                "bare_copy_gbs_aggregate": world * table_bytes / bare / 1e9,
-                               "e2e_gbs_per_rank": table_bytes / dt / 1e9, "frac": bare / dt}
+                               "e2e_gbs_per_rank": d2h_bytes / dt / 1e9,
+                               "table_gbs_delivered_per_rank": table_bytes / dt / 1e9,
+                               "frac": (d2h_bytes / dt) / (table_bytes / bare),
+                               "note": "frac = PCIe bytes actually moved per second / the bare copy rate; with the "
+                               "int16 transfer the rest of the step is the host threads' int32 stores"}
             del d_src, h_table
 
     secondary = None

@@ -312,11 +312,22 @@ int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n_frames, in
  * streams.  Uses the current device; `tile_rows` <= 0 picks a default.  Blocks
  * until the result is in host memory.  The cached workspace (streams, tile buffers) is
  * per device ordinal: calls for different devices run concurrently (one host thread per
- * GPU), calls for the same device serialise on that device's workspace. */
+ * GPU), calls for the same device serialise on that device's workspace.
+ * Narrow transfer: PCIe is the bound of this call (4 B per pixel and light direction).
+ * When the process has the host to itself (no LOCAL_WORLD_SIZE > 1) and >= 8 cores, a
+ * tile crosses PCIe as int16 (narrowed on the device, which also checks that every value
+ * fits; a tile with a value outside int16 is copied again as int32) into a pinned staging
+ * ring, and host threads sign-extend it into h_table while the next tile is in flight:
+ * same table, half the PCIe bytes, and h_table need not be pinned.
+ * RTI_HOST_TRANSFER=wide|narrow forces either form, RTI_HOST_THREADS the thread count
+ * (default: the affinity mask / LOCAL_WORLD_SIZE, at most 16). */
 int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cams, int n,
                          int rows_total, int cols, int row0, int rows,
                          const double *h_axis, int g,
                          int32_t *h_table, double *h_coef, int tile_rows);
+/* bytes the calling thread's last rti_ptm_compute_host moved device -> host (bench.py's
+ * e2e.d2h_bytes_per_step: half of the table's size when it crossed as int16) */
+int64_t rti_host_d2h_bytes(void);
 /* release the cached device workspace / streams of rti_ptm_compute_host */
 int rti_destroy(void);
 

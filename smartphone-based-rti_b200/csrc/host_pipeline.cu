@@ -2,10 +2,28 @@
 // (analysis.py:466-472): frames on the host in, int32 table / coefficients on the
 // host out.  The ROI slab is cut into row tiles; the H2D copy of tile t+1, the
 // fit + table kernels of tile t and the D2H copy of tile t-1 run on three streams.
+//
+// The int32 table is 4 B per pixel and light direction and PCIe is the end-to-end bound (42 GB per
+// 1024^2 ROI at ~55 GB/s).  Narrow transfer (default, RTI_HOST_TRANSFER=wide switches it off): the
+// tile is narrowed to int16 on the device (narrow_table_kernel, with a flag when a value does not
+// fit), crosses PCIe at half the bytes into a pinned staging ring, and host threads widen it into
+// the caller's table (host_widen.cpp) while the next tile is in flight; a tile whose flag is set is
+// copied again as int32 straight from the device tile, so the result is the same table either way.
+#include <condition_variable>
+#include <memory>
 #include <mutex>
+#include <sched.h>
+#include <stdlib.h>
+#include <thread>
+#include <vector>
 #include "common.cuh"
 
 namespace rti {
+
+void widen_i16_to_i32(const int16_t *src, int32_t *dst, size_t n);      // host_widen.cpp
+void widen_fence();
+
+constexpr int N_STAGE = 3;            // pinned int16 staging tiles: one filling by DMA, one being widened, one spare
 
 struct HostPipe {
     int device = -1;
@@ -17,6 +35,13 @@ struct HostPipe {
     double *d_cams = nullptr, *d_axis = nullptr;
     int32_t *d_bad = nullptr;           // [0] singular pixels, [1] unrepresentable values
     size_t frames_bytes = 0, coef_bytes = 0, table_bytes = 0, cams_bytes = 0, axis_bytes = 0;
+    // narrow transfer
+    int16_t *d_narrow[2] = {};
+    int32_t *d_flag = nullptr;          // [2]: tile of buffer b holds a value outside int16
+    int16_t *h_stage = nullptr;         // pinned, N_STAGE tiles
+    int32_t *h_flag = nullptr;          // pinned [N_STAGE]
+    cudaEvent_t ev_stage[N_STAGE] = {};
+    size_t narrow_bytes = 0, stage_bytes = 0;
     bool ready = false;
 };
 
@@ -45,6 +70,10 @@ static int pipe_release(HostPipe &c) {
         cudaEventDestroy(c.ev_comp[b]); cudaEventDestroy(c.ev_d2h[b]);
     }
     cudaFree(c.d_cams); cudaFree(c.d_axis); cudaFree(c.d_bad);
+    cudaFree(c.d_narrow[0]); cudaFree(c.d_narrow[1]); cudaFree(c.d_flag);
+    if (c.h_stage) cudaFreeHost(c.h_stage);
+    if (c.h_flag) cudaFreeHost(c.h_flag);
+    for (int s = 0; s < N_STAGE; ++s) cudaEventDestroy(c.ev_stage[s]);
     cudaStreamDestroy(c.s_h2d); cudaStreamDestroy(c.s_comp); cudaStreamDestroy(c.s_d2h);
     c = HostPipe();
     return RTI_OK;
@@ -62,14 +91,164 @@ static int pipe_init(HostPipe &c, int dev) {
         RTI_CUDA(cudaEventCreateWithFlags(&c.ev_comp[b], cudaEventDisableTiming));
         RTI_CUDA(cudaEventCreateWithFlags(&c.ev_d2h[b], cudaEventDisableTiming));
     }
+    // the host thread sleeps in cudaEventSynchronize on these instead of spinning: the cores belong to the wideners
+    for (int s = 0; s < N_STAGE; ++s)
+        RTI_CUDA(cudaEventCreateWithFlags(&c.ev_stage[s], cudaEventDisableTiming | cudaEventBlockingSync));
     RTI_CUDA(cudaMalloc(&c.d_bad, 2 * sizeof(int32_t)));
+    RTI_CUDA(cudaMalloc(&c.d_flag, 2 * sizeof(int32_t)));
+    RTI_CUDA(cudaHostAlloc(&c.h_flag, N_STAGE * sizeof(int32_t), cudaHostAllocDefault));
     c.ready = true;
     return RTI_OK;
 }
 
+// int32 table tile [gg][image_stride] -> int16 [gg][tp] (packed: one contiguous D2H copy); *flag |= 1 when a value
+// is outside [-limit - 1, limit] (limit = 32767 unless a test lowers it).  Thread = 8 consecutive pixels of one
+// image (two 16-byte loads, one 16-byte store) when the shapes allow it.
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+narrow_table_kernel(const int32_t *__restrict__ table, int64_t image_stride, int64_t tp, int64_t gg, int limit,
+                    int16_t *__restrict__ out, int32_t *__restrict__ flag) {
+    bool over = false;
+    const int64_t x0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * (VEC ? 8 : 1);
+    if (x0 < tp) {
+        for (int64_t i = blockIdx.y; i < gg; i += gridDim.y) {
+            const int32_t *src = table + i * image_stride + x0;
+            int16_t *dst = out + i * tp + x0;
+            if (VEC) {
+                const int4 a = __ldcs(reinterpret_cast<const int4 *>(src));
+                const int4 b = __ldcs(reinterpret_cast<const int4 *>(src) + 1);
+                const int v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+                for (int k = 0; k < 8; ++k) over |= (v[k] > limit) | (v[k] < -limit - 1);
+                int4 o;
+                o.x = (v[0] & 0xffff) | (v[1] << 16);
+                o.y = (v[2] & 0xffff) | (v[3] << 16);
+                o.z = (v[4] & 0xffff) | (v[5] << 16);
+                o.w = (v[6] & 0xffff) | (v[7] << 16);
+                __stcs(reinterpret_cast<int4 *>(dst), o);
+            } else {
+                const int v = __ldcs(src);
+                over |= (v > limit) | (v < -limit - 1);
+                *dst = (int16_t)v;
+            }
+        }
+    }
+    if (__any_sync(0xffffffffu, over) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
+}
+
+static int launch_narrow(const int32_t *d_table, int64_t image_stride, int64_t tp, int64_t gg, int limit,
+                         int16_t *d_out, int32_t *d_flag, cudaStream_t stream) {
+    const bool vec = tp % 8 == 0 && image_stride % 4 == 0;
+    const int64_t items = vec ? tp / 8 : tp;
+    const unsigned bx = (unsigned)((items + 255) / 256);
+    const unsigned by = (unsigned)(gg < 32768 ? gg : 32768);
+    if (vec) narrow_table_kernel<true><<<dim3(bx, by), 256, 0, stream>>>(d_table, image_stride, tp, gg, limit, d_out, d_flag);
+    else narrow_table_kernel<false><<<dim3(bx, by), 256, 0, stream>>>(d_table, image_stride, tp, gg, limit, d_out, d_flag);
+    RTI_LAUNCHED("narrow_table_kernel");
+    return RTI_OK;
+}
+
+// Host threads that widen staged int16 tiles into the caller's int32 table, tile by tile in the order they
+// are published; thread j owns images [gg j / T, gg (j + 1) / T) of every tile.  The destructor stops and
+// joins them, so an early error return of the caller cannot leave threads behind.
+class Wideners {
+public:
+    struct Job { const int16_t *src; int64_t pix_off, tp; bool skip; };
+    Wideners(int threads, int64_t n_tiles, int64_t gg, int64_t slab_pixels, int32_t *h_table)
+        : jobs_((size_t)n_tiles), left_((size_t)n_tiles, threads), n_tiles_(n_tiles), gg_(gg),
+          slab_pixels_(slab_pixels), h_table_(h_table), threads_(threads) {
+        for (int j = 0; j < threads; ++j) th_.emplace_back([this, j] { run(j); });
+    }
+    ~Wideners() {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            abort_ = true;
+        }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+    void publish(const Job &job) {                       // the next tile is in its staging buffer (or skipped)
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            jobs_[(size_t)published_] = job;
+            ++published_;
+        }
+        cv_.notify_all();
+    }
+    void wait_done(int64_t tiles) {                      // blocks until the first `tiles` tiles are in h_table
+        std::unique_lock<std::mutex> lk(m_);
+        cv_.wait(lk, [&] { return done_ >= tiles; });
+    }
+
+private:
+    void run(int j) {
+        const int64_t i0 = gg_ * j / threads_, i1 = gg_ * (j + 1) / threads_;
+        for (int64_t k = 0; k < n_tiles_; ++k) {
+            Job job;
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [&] { return abort_ || published_ > k; });
+                if (published_ <= k) return;             // aborted before this tile arrived
+                job = jobs_[(size_t)k];
+            }
+            if (!job.skip) {
+                for (int64_t i = i0; i < i1; ++i)
+                    widen_i16_to_i32(job.src + i * job.tp, h_table_ + i * slab_pixels_ + job.pix_off, (size_t)job.tp);
+                widen_fence();
+            }
+            bool last;
+            {
+                std::lock_guard<std::mutex> lk(m_);
+                last = --left_[(size_t)k] == 0;
+                if (last) done_ = k + 1;                 // tiles finish in order: every thread walks them in order
+            }
+            if (last) cv_.notify_all();
+        }
+    }
+    std::vector<std::thread> th_;
+    std::vector<Job> jobs_;
+    std::vector<int> left_;
+    std::mutex m_;
+    std::condition_variable cv_;
+    int64_t published_ = 0, done_ = 0, n_tiles_, gg_, slab_pixels_;
+    int32_t *h_table_;
+    int threads_;
+    bool abort_ = false;
+};
+
+// Cores this process may use for widening: RTI_HOST_THREADS, else the affinity mask shared out between the
+// ranks of this host (torchrun's LOCAL_WORLD_SIZE), at most 16.
+static int local_world() {
+    const char *e = getenv("LOCAL_WORLD_SIZE");
+    const int w = e ? atoi(e) : 1;
+    return w > 0 ? w : 1;
+}
+static int widen_threads() {
+    const char *e = getenv("RTI_HOST_THREADS");
+    if (e && atoi(e) > 0) return atoi(e) < 64 ? atoi(e) : 64;
+    cpu_set_t set;
+    int cores = sched_getaffinity(0, sizeof(set), &set) == 0 ? CPU_COUNT(&set) : (int)std::thread::hardware_concurrency();
+    cores /= local_world();
+    return cores < 1 ? 1 : (cores > 16 ? 16 : cores);
+}
+// narrow transfer: RTI_HOST_TRANSFER=narrow|wide, else when this process has the host to itself and >= 8 cores.
+// (With several ranks per host the shared limit is the host's memory path, which the int32 stores of the
+// widening load as much as the DMA writes they replace: measured 91 GB/s of DMA for 8 ranks, ~105 GB/s of
+// widening stores on 16 cores.)
+static bool want_narrow() {
+    const char *e = getenv("RTI_HOST_TRANSFER");
+    if (e && e[0] == 'n') return true;
+    if (e && e[0] == 'w') return false;
+    return local_world() == 1 && widen_threads() >= 8;
+}
+
+static thread_local int64_t t_last_d2h_bytes = 0;
+
 }  // namespace rti
 
 using namespace rti;
+
+extern "C" int64_t rti_host_d2h_bytes(void) { return t_last_d2h_bytes; }
 
 extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cams, int n, int rows_total,
                                     int cols, int row0, int rows, const double *h_axis, int g,
@@ -106,58 +285,119 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
     const int64_t tile_pixels = (int64_t)tile_rows * cols;
     const int64_t slab_pixels = (int64_t)rows * cols;
     const int64_t frame_pitch = (int64_t)rows_total * cols;
+    const int64_t n_tiles = (rows + tile_rows - 1) / tile_rows;
+    const bool narrow = h_table != nullptr && want_narrow();
+    const char *env_limit = getenv("RTI_HOST_NARROW_LIMIT");              // tests lower it to force the int32 re-copy
+    const int limit = env_limit && atoi(env_limit) > 0 && atoi(env_limit) < 32767 ? atoi(env_limit) : 32767;
 
     for (int b = 0; b < 2; ++b) {
-        size_t fb = c.frames_bytes, cb = c.coef_bytes, tb = c.table_bytes;
+        size_t fb = c.frames_bytes, cb = c.coef_bytes, tb = c.table_bytes, nb = c.narrow_bytes;
         if ((rc = grow((void **)&c.d_frames[b], &fb, (size_t)n * tile_pixels)) != RTI_OK) return rc;
         if ((rc = grow((void **)&c.d_coef[b], &cb, (size_t)6 * tile_pixels * sizeof(double))) != RTI_OK) return rc;
         if (h_table && (rc = grow((void **)&c.d_table[b], &tb, (size_t)gg * tile_pixels * sizeof(int32_t))) != RTI_OK) return rc;
-        if (b == 1) { c.frames_bytes = fb; c.coef_bytes = cb; if (h_table) c.table_bytes = tb; }
+        if (narrow && (rc = grow((void **)&c.d_narrow[b], &nb, (size_t)gg * tile_pixels * sizeof(int16_t))) != RTI_OK) return rc;
+        if (b == 1) { c.frames_bytes = fb; c.coef_bytes = cb; if (h_table) c.table_bytes = tb; if (narrow) c.narrow_bytes = nb; }
     }
     if ((rc = grow((void **)&c.d_cams, &c.cams_bytes, (size_t)n * 3 * sizeof(double))) != RTI_OK) return rc;
     if ((rc = grow((void **)&c.d_axis, &c.axis_bytes, (size_t)g * sizeof(double))) != RTI_OK) return rc;
+    const size_t stage_elems = (size_t)gg * tile_pixels;                   // int16 per staging tile
+    if (narrow && c.stage_bytes < N_STAGE * stage_elems * sizeof(int16_t)) {
+        if (c.h_stage) RTI_CUDA(cudaFreeHost(c.h_stage));
+        c.h_stage = nullptr;
+        c.stage_bytes = 0;
+        RTI_CUDA(cudaHostAlloc(&c.h_stage, N_STAGE * stage_elems * sizeof(int16_t), cudaHostAllocDefault));
+        c.stage_bytes = N_STAGE * stage_elems * sizeof(int16_t);
+    }
 
     RTI_CUDA(cudaMemsetAsync(c.d_bad, 0, 2 * sizeof(int32_t), c.s_comp));
     RTI_CUDA(cudaMemcpyAsync(c.d_cams, h_cams, (size_t)n * 3 * sizeof(double), cudaMemcpyHostToDevice, c.s_comp));
     RTI_CUDA(cudaMemcpyAsync(c.d_axis, h_axis, (size_t)g * sizeof(double), cudaMemcpyHostToDevice, c.s_comp));
 
-    int t = 0;
-    for (int r = 0; r < rows; r += tile_rows, ++t) {
-        const int b = t & 1;
-        const int tr = (rows - r < tile_rows) ? rows - r : tile_rows;
-        const int64_t tp = (int64_t)tr * cols;
-        const int64_t pix_off = (int64_t)r * cols;                    // within the slab
-        // ---- H2D: n rows of tp bytes, host pitch = one full frame
-        if (t >= 2) RTI_CUDA(cudaStreamWaitEvent(c.s_h2d, c.ev_fit[b], 0));   // frames[b] free again
-        RTI_CUDA(cudaMemcpy2DAsync(c.d_frames[b], (size_t)tile_pixels,
-                                   h_frames + (int64_t)(row0 + r) * cols, (size_t)frame_pitch,
-                                   (size_t)tp, (size_t)n, cudaMemcpyHostToDevice, c.s_h2d));
-        RTI_CUDA(cudaEventRecord(c.ev_h2d[b], c.s_h2d));
-        // ---- compute
-        RTI_CUDA(cudaStreamWaitEvent(c.s_comp, c.ev_h2d[b], 0));
-        if (t >= 2) RTI_CUDA(cudaStreamWaitEvent(c.s_comp, c.ev_d2h[b], 0));  // coef[b]/table[b] drained
-        if (h_table) {
-            rc = rti_ptm_fit_table_frames(c.d_frames[b], tile_pixels, c.d_cams, n, row0 + r, tr, cols, c.d_axis, g,
-                                          c.d_coef[b], tile_pixels, c.d_table[b], tile_pixels, c.d_bad, c.s_comp);
-        } else {
-            rc = rti_ptm_fit_frames(c.d_frames[b], tile_pixels, c.d_cams, n, row0 + r, tr, cols, c.d_coef[b],
-                                    tile_pixels, c.d_bad, c.s_comp);
+    int64_t d2h_bytes = 0;
+    {
+        // declared before the loop: its destructor joins the threads on every way out of this block
+        std::unique_ptr<Wideners> wide(narrow ? new Wideners(widen_threads(), n_tiles, gg, slab_pixels, h_table) : nullptr);
+        // a staged tile is handed to the wideners one iteration after it was queued, so the GPU always has the
+        // next tile's copies queued behind the one the host waits for
+        auto hand_over = [&](int64_t k) -> int {
+            const int b = (int)(k & 1), sb = (int)(k % N_STAGE);
+            const int r = (int)(k * tile_rows);
+            const int tr = (rows - r < tile_rows) ? rows - r : tile_rows;
+            const int64_t tp = (int64_t)tr * cols, pix_off = (int64_t)r * cols;
+            RTI_CUDA(cudaEventSynchronize(c.ev_stage[sb]));
+            const bool over = c.h_flag[sb] != 0;
+            if (over) {            // a value outside int16: this tile again, as int32 (its device tile is still intact)
+                RTI_CUDA(cudaMemcpy2DAsync(h_table + pix_off, (size_t)slab_pixels * sizeof(int32_t), c.d_table[b],
+                                           (size_t)tile_pixels * sizeof(int32_t), (size_t)tp * sizeof(int32_t),
+                                           (size_t)gg, cudaMemcpyDeviceToHost, c.s_d2h));
+                RTI_CUDA(cudaStreamSynchronize(c.s_d2h));
+                d2h_bytes += gg * tp * (int64_t)sizeof(int32_t);
+            }
+            wide->publish({c.h_stage + (size_t)sb * stage_elems, pix_off, tp, over});
+            return RTI_OK;
+        };
+        for (int64_t t = 0; t < n_tiles; ++t) {
+            const int b = (int)(t & 1), sb = (int)(t % N_STAGE);
+            const int r = (int)(t * tile_rows);
+            const int tr = (rows - r < tile_rows) ? rows - r : tile_rows;
+            const int64_t tp = (int64_t)tr * cols;
+            const int64_t pix_off = (int64_t)r * cols;                    // within the slab
+            // ---- H2D: n rows of tp bytes, host pitch = one full frame
+            if (t >= 2) RTI_CUDA(cudaStreamWaitEvent(c.s_h2d, c.ev_fit[b], 0));   // frames[b] free again
+            RTI_CUDA(cudaMemcpy2DAsync(c.d_frames[b], (size_t)tile_pixels,
+                                       h_frames + (int64_t)(row0 + r) * cols, (size_t)frame_pitch,
+                                       (size_t)tp, (size_t)n, cudaMemcpyHostToDevice, c.s_h2d));
+            RTI_CUDA(cudaEventRecord(c.ev_h2d[b], c.s_h2d));
+            // ---- compute
+            RTI_CUDA(cudaStreamWaitEvent(c.s_comp, c.ev_h2d[b], 0));
+            if (t >= 2) RTI_CUDA(cudaStreamWaitEvent(c.s_comp, c.ev_d2h[b], 0));  // coef[b]/table[b]/narrow[b] drained
+            if (h_table) {
+                rc = rti_ptm_fit_table_frames(c.d_frames[b], tile_pixels, c.d_cams, n, row0 + r, tr, cols, c.d_axis, g,
+                                              c.d_coef[b], tile_pixels, c.d_table[b], tile_pixels, c.d_bad, c.s_comp);
+            } else {
+                rc = rti_ptm_fit_frames(c.d_frames[b], tile_pixels, c.d_cams, n, row0 + r, tr, cols, c.d_coef[b],
+                                        tile_pixels, c.d_bad, c.s_comp);
+            }
+            if (rc != RTI_OK) return rc;
+            RTI_CUDA(cudaEventRecord(c.ev_fit[b], c.s_comp));
+            if (narrow) {
+                RTI_CUDA(cudaMemsetAsync(c.d_flag + b, 0, sizeof(int32_t), c.s_comp));
+                if ((rc = launch_narrow(c.d_table[b], tile_pixels, tp, gg, limit, c.d_narrow[b], c.d_flag + b, c.s_comp)) != RTI_OK)
+                    return rc;
+            }
+            RTI_CUDA(cudaEventRecord(c.ev_comp[b], c.s_comp));
+            // ---- D2H
+            RTI_CUDA(cudaStreamWaitEvent(c.s_d2h, c.ev_comp[b], 0));
+            if (narrow) {
+                wide->wait_done(t - N_STAGE + 1);                         // staging tile sb has been widened
+                RTI_CUDA(cudaMemcpyAsync(c.h_stage + (size_t)sb * stage_elems, c.d_narrow[b],
+                                         (size_t)gg * tp * sizeof(int16_t), cudaMemcpyDeviceToHost, c.s_d2h));
+                RTI_CUDA(cudaMemcpyAsync(c.h_flag + sb, c.d_flag + b, sizeof(int32_t), cudaMemcpyDeviceToHost, c.s_d2h));
+                d2h_bytes += gg * tp * (int64_t)sizeof(int16_t);
+            } else if (h_table) {
+                RTI_CUDA(cudaMemcpy2DAsync(h_table + pix_off, (size_t)slab_pixels * sizeof(int32_t), c.d_table[b],
+                                           (size_t)tile_pixels * sizeof(int32_t), (size_t)tp * sizeof(int32_t),
+                                           (size_t)gg, cudaMemcpyDeviceToHost, c.s_d2h));
+                d2h_bytes += gg * tp * (int64_t)sizeof(int32_t);
+            }
+            if (h_coef) {
+                RTI_CUDA(cudaMemcpy2DAsync(h_coef + pix_off, (size_t)slab_pixels * sizeof(double), c.d_coef[b],
+                                           (size_t)tile_pixels * sizeof(double), (size_t)tp * sizeof(double), 6,
+                                           cudaMemcpyDeviceToHost, c.s_d2h));
+                d2h_bytes += 6 * tp * (int64_t)sizeof(double);
+            }
+            RTI_CUDA(cudaEventRecord(c.ev_d2h[b], c.s_d2h));
+            if (narrow) {
+                RTI_CUDA(cudaEventRecord(c.ev_stage[sb], c.s_d2h));
+                if (t >= 1 && (rc = hand_over(t - 1)) != RTI_OK) return rc;
+            }
         }
-        if (rc != RTI_OK) return rc;
-        RTI_CUDA(cudaEventRecord(c.ev_fit[b], c.s_comp));
-        RTI_CUDA(cudaEventRecord(c.ev_comp[b], c.s_comp));
-        // ---- D2H
-        RTI_CUDA(cudaStreamWaitEvent(c.s_d2h, c.ev_comp[b], 0));
-        if (h_table)
-            RTI_CUDA(cudaMemcpy2DAsync(h_table + pix_off, (size_t)slab_pixels * sizeof(int32_t), c.d_table[b],
-                                       (size_t)tile_pixels * sizeof(int32_t), (size_t)tp * sizeof(int32_t),
-                                       (size_t)gg, cudaMemcpyDeviceToHost, c.s_d2h));
-        if (h_coef)
-            RTI_CUDA(cudaMemcpy2DAsync(h_coef + pix_off, (size_t)slab_pixels * sizeof(double), c.d_coef[b],
-                                       (size_t)tile_pixels * sizeof(double), (size_t)tp * sizeof(double), 6,
-                                       cudaMemcpyDeviceToHost, c.s_d2h));
-        RTI_CUDA(cudaEventRecord(c.ev_d2h[b], c.s_d2h));
+        if (narrow) {
+            if ((rc = hand_over(n_tiles - 1)) != RTI_OK) return rc;
+            wide->wait_done(n_tiles);
+        }
     }
+    t_last_d2h_bytes = d2h_bytes;
     int32_t bad[2] = {0, 0};
     RTI_CUDA(cudaStreamSynchronize(c.s_d2h));
     RTI_CUDA(cudaMemcpyAsync(bad, c.d_bad, sizeof(bad), cudaMemcpyDeviceToHost, c.s_comp));

@@ -473,27 +473,52 @@ def test_compute_from_storage_writes_reference_pickle(torch_cuda, ref_small, mon
     values[values <= 0] = 0
 
 
-def test_host_pipeline_tiles_match_single_shot(torch_cuda):
-    """rti_ptm_compute_host with many small row tiles == device path on the whole slab."""
+@pytest.mark.parametrize("transfer,limit,threads,pinned", [
+    ("wide", None, None, True),          # int32 tiles straight into the caller's pinned table
+    ("narrow", None, None, True),        # int16 over PCIe + host widening threads
+    ("narrow", None, "3", False),        # pageable destination, image ranges that do not divide evenly
+    ("narrow", "100", "2", True),        # most tiles hold a value beyond the (lowered) limit: int32 re-copy
+    (None, None, None, True),            # the library's own choice for this host
+])
+def test_host_pipeline_tiles_match_single_shot(torch_cuda, monkeypatch, transfer, limit, threads, pinned):
+    """rti_ptm_compute_host with many small row tiles == device path on the whole slab, in both transfer
+    forms (the table that reaches the host is the same int32 table either way)."""
     from rti_b200 import _capi, synthetic
     torch = torch_cuda
-    rows_total, cols, n, row0, rows = 23, 36, 61, 5, 14
+    for name, val in (("RTI_HOST_TRANSFER", transfer), ("RTI_HOST_NARROW_LIMIT", limit), ("RTI_HOST_THREADS", threads)):
+        if val is None:
+            monkeypatch.delenv(name, raising=False)
+        else:
+            monkeypatch.setenv(name, val)
+    rows_total, cols, n, row0, rows = 23, 36, 61, 5, 15
     frames, cams = synthetic.lambertian_stack(rows_total, cols, n, seed=21)
     ax = orc.light_axis(0.1)
     g = ax.size
     p = rows * cols
-    h_table = torch.empty((g, g, p), dtype=torch.int32).pin_memory()
+    h_table = torch.empty((g, g, p), dtype=torch.int32)
     h_coef = torch.empty((6, p), dtype=torch.float64).pin_memory()
+    if pinned:
+        h_table = h_table.pin_memory()
     h_frames = torch.from_numpy(frames).pin_memory()
-    for tile_rows in (3, 0):
+    lx, ly, inten = orc.gather_soa(frames, cams)
+    ref = orc.ptm_fit_batch(lx[row0:row0 + rows], ly[row0:row0 + rows], inten[row0:row0 + rows]).reshape(-1, 6)
+    ref_tab = orc.table_from_grids(orc.ptm_grid(ref, ax).reshape(p, 1, g, g))[:, :, :, 0]
+    if limit is not None:
+        assert np.abs(ref_tab).max() > int(limit)                         # the re-copy path is really taken
+    # tiles of 4 rows (144 px: vector narrowing; last tile 3 rows = 108 px: scalar), one tile of 540 px, 8 + 7 rows
+    for tile_rows in (3, 0, 5):
         h_table.fill_(-1)
+        h_coef.fill_(0)
         _capi.call("rti_ptm_compute_host", h_frames.data_ptr(), cams.ctypes.data, n, rows_total, cols, row0, rows,
                    ax.ctypes.data, g, h_table.data_ptr(), h_coef.data_ptr(), tile_rows)
-        lx, ly, inten = orc.gather_soa(frames, cams)
-        ref = orc.ptm_fit_batch(lx[row0:row0 + rows], ly[row0:row0 + rows], inten[row0:row0 + rows]).reshape(-1, 6)
         assert coef_rel_err(h_coef.numpy().T, ref) < PTM_COEF_RTOL
-        ref_tab = orc.table_from_grids(orc.ptm_grid(ref, ax).reshape(p, 1, g, g))[:, :, :, 0]
         assert np.count_nonzero(h_table.numpy() != ref_tab) == 0
+        moved = _capi.load().rti_host_d2h_bytes()
+        wide_bytes = 4 * g * g * p + 48 * p
+        if transfer == "wide":
+            assert moved == wide_bytes
+        elif transfer == "narrow" and limit is None:
+            assert moved == 2 * g * g * p + 48 * p
     _capi.call("rti_destroy")
 
 
