@@ -13,6 +13,7 @@
 #include <memory>
 #include <mutex>
 #include <sched.h>
+#include <stdexcept>
 #include <stdlib.h>
 #include <thread>
 #include <vector>
@@ -157,16 +158,14 @@ public:
     Wideners(int threads, int64_t n_tiles, int64_t gg, int64_t slab_pixels, int32_t *h_table)
         : jobs_((size_t)n_tiles), left_((size_t)n_tiles, threads), n_tiles_(n_tiles), gg_(gg),
           slab_pixels_(slab_pixels), h_table_(h_table), threads_(threads) {
-        for (int j = 0; j < threads; ++j) th_.emplace_back([this, j] { run(j); });
-    }
-    ~Wideners() {
-        {
-            std::lock_guard<std::mutex> lk(m_);
-            abort_ = true;
+        try {
+            for (int j = 0; j < threads; ++j) th_.emplace_back([this, j] { run(j); });
+        } catch (...) {
+            stop();                                      // the threads that did start
+            throw;
         }
-        cv_.notify_all();
-        for (auto &t : th_) t.join();
     }
+    ~Wideners() { stop(); }
     void publish(const Job &job) {                       // the next tile is in its staging buffer (or skipped)
         {
             std::lock_guard<std::mutex> lk(m_);
@@ -181,6 +180,15 @@ public:
     }
 
 private:
+    void stop() {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            abort_ = true;
+        }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+        th_.clear();
+    }
     void run(int j) {
         const int64_t i0 = gg_ * j / threads_, i1 = gg_ * (j + 1) / threads_;
         for (int64_t k = 0; k < n_tiles_; ++k) {
@@ -316,7 +324,16 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
     int64_t d2h_bytes = 0;
     {
         // declared before the loop: its destructor joins the threads on every way out of this block
-        std::unique_ptr<Wideners> wide(narrow ? new Wideners(widen_threads(), n_tiles, gg, slab_pixels, h_table) : nullptr);
+        std::unique_ptr<Wideners> wide;
+        if (narrow) {
+            try {
+                wide.reset(new Wideners(widen_threads(), n_tiles, gg, slab_pixels, h_table));
+            } catch (const std::exception &e) {           // no threads to be had: say so instead of terminating
+                set_error("rti_ptm_compute_host: cannot start the widening threads (%s); RTI_HOST_TRANSFER=wide avoids them",
+                          e.what());
+                return RTI_ERR_ARG;
+            }
+        }
         // a staged tile is handed to the wideners one iteration after it was queued, so the GPU always has the
         // next tile's copies queued behind the one the host waits for
         auto hand_over = [&](int64_t k) -> int {
