@@ -9,20 +9,15 @@
 // fit), crosses PCIe at half the bytes into a pinned staging ring, and host threads widen it into
 // the caller's table (host_widen.cpp) while the next tile is in flight; a tile whose flag is set is
 // copied again as int32 straight from the device tile, so the result is the same table either way.
-#include <condition_variable>
 #include <memory>
 #include <mutex>
 #include <sched.h>
 #include <stdexcept>
 #include <stdlib.h>
-#include <thread>
-#include <vector>
 #include "common.cuh"
+#include "host_widen.h"
 
 namespace rti {
-
-void widen_i16_to_i32(const int16_t *src, int32_t *dst, size_t n);      // host_widen.cpp
-void widen_fence();
 
 constexpr int N_STAGE = 3;            // pinned int16 staging tiles: one filling by DMA, one being widened, one spare
 
@@ -148,81 +143,6 @@ static int launch_narrow(const int32_t *d_table, int64_t image_stride, int64_t t
     RTI_LAUNCHED("narrow_table_kernel");
     return RTI_OK;
 }
-
-// Host threads that widen staged int16 tiles into the caller's int32 table, tile by tile in the order they
-// are published; thread j owns images [gg j / T, gg (j + 1) / T) of every tile.  The destructor stops and
-// joins them, so an early error return of the caller cannot leave threads behind.
-class Wideners {
-public:
-    struct Job { const int16_t *src; int64_t pix_off, tp; bool skip; };
-    Wideners(int threads, int64_t n_tiles, int64_t gg, int64_t slab_pixels, int32_t *h_table)
-        : jobs_((size_t)n_tiles), left_((size_t)n_tiles, threads), n_tiles_(n_tiles), gg_(gg),
-          slab_pixels_(slab_pixels), h_table_(h_table), threads_(threads) {
-        try {
-            for (int j = 0; j < threads; ++j) th_.emplace_back([this, j] { run(j); });
-        } catch (...) {
-            stop();                                      // the threads that did start
-            throw;
-        }
-    }
-    ~Wideners() { stop(); }
-    void publish(const Job &job) {                       // the next tile is in its staging buffer (or skipped)
-        {
-            std::lock_guard<std::mutex> lk(m_);
-            jobs_[(size_t)published_] = job;
-            ++published_;
-        }
-        cv_.notify_all();
-    }
-    void wait_done(int64_t tiles) {                      // blocks until the first `tiles` tiles are in h_table
-        std::unique_lock<std::mutex> lk(m_);
-        cv_.wait(lk, [&] { return done_ >= tiles; });
-    }
-
-private:
-    void stop() {
-        {
-            std::lock_guard<std::mutex> lk(m_);
-            abort_ = true;
-        }
-        cv_.notify_all();
-        for (auto &t : th_) t.join();
-        th_.clear();
-    }
-    void run(int j) {
-        const int64_t i0 = gg_ * j / threads_, i1 = gg_ * (j + 1) / threads_;
-        for (int64_t k = 0; k < n_tiles_; ++k) {
-            Job job;
-            {
-                std::unique_lock<std::mutex> lk(m_);
-                cv_.wait(lk, [&] { return abort_ || published_ > k; });
-                if (published_ <= k) return;             // aborted before this tile arrived
-                job = jobs_[(size_t)k];
-            }
-            if (!job.skip) {
-                for (int64_t i = i0; i < i1; ++i)
-                    widen_i16_to_i32(job.src + i * job.tp, h_table_ + i * slab_pixels_ + job.pix_off, (size_t)job.tp);
-                widen_fence();
-            }
-            bool last;
-            {
-                std::lock_guard<std::mutex> lk(m_);
-                last = --left_[(size_t)k] == 0;
-                if (last) done_ = k + 1;                 // tiles finish in order: every thread walks them in order
-            }
-            if (last) cv_.notify_all();
-        }
-    }
-    std::vector<std::thread> th_;
-    std::vector<Job> jobs_;
-    std::vector<int> left_;
-    std::mutex m_;
-    std::condition_variable cv_;
-    int64_t published_ = 0, done_ = 0, n_tiles_, gg_, slab_pixels_;
-    int32_t *h_table_;
-    int threads_;
-    bool abort_ = false;
-};
 
 // Cores this process may use for widening: RTI_HOST_THREADS, else the affinity mask shared out between the
 // ranks of this host (torchrun's LOCAL_WORLD_SIZE), at most 16.

@@ -4,8 +4,7 @@
 // Plain C++ (compiled by the host compiler, not cudafe) so the AVX2 path can use intrinsics;
 // non-temporal stores: the destination (tens of GB) is written once and not read back here.
 #include <immintrin.h>
-#include <stddef.h>
-#include <stdint.h>
+#include "host_widen.h"
 
 namespace rti {
 

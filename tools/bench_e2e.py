@@ -52,7 +52,8 @@ def main():
             os.environ["RTI_HOST_TRANSFER"] = parts[0]
         if len(parts) > 1:
             os.environ["RTI_HOST_THREADS"] = parts[1]
-        pageable = len(parts) > 2
+        pageable = "pageable" in parts[2:]
+        tile_rows = ([int(x[2:]) for x in parts[2:] if x.startswith("tr")] or [0])[0]   # e.g. narrow:16:tr2
         if pageable and h_pageable is None:
             h_pageable = torch.empty((g, g, p), dtype=torch.int32)
             h_pageable.fill_(0)                                   # touch the pages
@@ -60,7 +61,7 @@ def main():
 
         def step():
             _capi.call("rti_ptm_compute_host", h_frames.data_ptr(), cams.ctypes.data, n, rows, cols, 0, rows,
-                       axis.ctypes.data, g, h_table.data_ptr(), None, 0)
+                       axis.ctypes.data, g, h_table.data_ptr(), None, tile_rows)
         step()
         t0 = time.perf_counter()
         for _ in range(args.steps):

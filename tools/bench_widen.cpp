@@ -1,31 +1,94 @@
+// Host-only driver for the widening half of the narrow transfer (csrc/host_widen.h, host_widen.cpp):
+//   widen_bench --check     correctness: widen_i16_to_i32 at every alignment / ragged length, and the Wideners
+//                           thread protocol (tiles in order, skipped tiles untouched, early destruction) against
+//                           a plain loop; prints "check ok" (tests/test_host_widen.py builds and runs this)
+//   widen_bench T           throughput of T threads widening 2 GiB of int16 into 4 GiB of int32
+//   g++ -O3 -std=c++17 -pthread tools/bench_widen.cpp smartphone-based-rti_b200/csrc/host_widen.cpp -o scratch/widen_bench
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
-#include <cstdint>
-#include <vector>
-#include <thread>
-#include <chrono>
 #include <cstring>
-namespace rti { void widen_i16_to_i32(const int16_t*, int32_t*, size_t); void widen_fence(); }
-int main(int argc, char** argv) {
-    int T = argc > 1 ? atoi(argv[1]) : 8;
-    // correctness at odd alignments and lengths
-    for (int off = 0; off < 9; ++off) for (size_t n : {0, 1, 7, 8, 31, 32, 33, 100, 1000, 4099}) {
-        std::vector<int16_t> s(n + 16); std::vector<int32_t> d(n + 32, 0x7fffffff);
-        for (size_t i = 0; i < s.size(); ++i) s[i] = (int16_t)(i * 2654435761u >> 7);
-        rti::widen_i16_to_i32(s.data() + off % 3, d.data() + off, n);
-        for (size_t i = 0; i < n; ++i) if (d[off + i] != s[off % 3 + i]) { printf("MISMATCH off %d n %zu i %zu\n", off, n, i); return 1; }
-        if (d[off + n] != 0x7fffffff || (off && d[off - 1] != 0x7fffffff)) { printf("OVERRUN\n"); return 1; }
+#include <random>
+#include "../smartphone-based-rti_b200/csrc/host_widen.h"
+
+static int check() {
+    // ---- the kernel of it: any alignment of either pointer, lengths around the vector widths
+    for (int off = 0; off < 9; ++off)
+        for (size_t n : {0, 1, 7, 8, 15, 16, 31, 32, 33, 63, 100, 1000, 4099}) {
+            std::vector<int16_t> s(n + 16);
+            std::vector<int32_t> d(n + 32, 0x7fffffff);
+            for (size_t i = 0; i < s.size(); ++i) s[i] = (int16_t)((i + 1) * 2654435761u >> 7);
+            if (n > 2) { s[off % 3] = -32768; s[off % 3 + 1] = 32767; }
+            rti::widen_i16_to_i32(s.data() + off % 3, d.data() + off, n);
+            for (size_t i = 0; i < n; ++i)
+                if (d[off + i] != s[off % 3 + i]) { printf("MISMATCH off %d n %zu i %zu\n", off, n, i); return 1; }
+            if (d[off + n] != 0x7fffffff || (off && d[off - 1] != 0x7fffffff)) { printf("OVERRUN off %d n %zu\n", off, n); return 1; }
+        }
+    // ---- the thread protocol: a slab of `slab` pixels per image, cut into ragged tiles; some tiles are
+    // skipped (the caller re-copied them as int32) and must stay untouched; staging buffers are reused
+    // three tiles later, which is only safe once wait_done() says so
+    std::mt19937 rng(7);
+    for (int trial = 0; trial < 24; ++trial) {
+        const int threads = 1 + (int)(rng() % 7);
+        const int64_t gg = 1 + (int64_t)(rng() % 37);                      // also fewer images than threads
+        const int64_t n_tiles = 1 + (int64_t)(rng() % 9);
+        std::vector<int64_t> tp((size_t)n_tiles), off((size_t)n_tiles);
+        int64_t slab = 0;
+        for (int64_t k = 0; k < n_tiles; ++k) { off[(size_t)k] = slab; tp[(size_t)k] = 1 + (int64_t)(rng() % 300); slab += tp[(size_t)k]; }
+        std::vector<int32_t> table((size_t)(gg * slab), -7), ref((size_t)(gg * slab), -7);
+        int64_t tp_max = 0;
+        for (auto v : tp) tp_max = v > tp_max ? v : tp_max;
+        std::vector<int16_t> stage((size_t)(3 * gg * tp_max));
+        {
+            rti::Wideners w(threads, n_tiles, gg, slab, table.data());
+            for (int64_t k = 0; k < n_tiles; ++k) {
+                w.wait_done(k - 2);                                        // staging buffer k % 3 is free again
+                int16_t *buf = stage.data() + (size_t)((k % 3) * gg * tp_max);
+                const bool skip = rng() % 4 == 0;
+                for (int64_t i = 0; i < gg; ++i)
+                    for (int64_t x = 0; x < tp[(size_t)k]; ++x) {
+                        const int16_t v = (int16_t)(rng() & 0xffff);
+                        buf[i * tp[(size_t)k] + x] = v;
+                        if (!skip) ref[(size_t)(i * slab + off[(size_t)k] + x)] = v;
+                    }
+                w.publish({buf, off[(size_t)k], tp[(size_t)k], skip});
+            }
+            w.wait_done(n_tiles);
+        }
+        if (table != ref) { printf("WIDENERS MISMATCH trial %d\n", trial); return 1; }
     }
-    printf("correct\n");
-    size_t total = (size_t)1 << 30;     // elements: 2 GiB in, 4 GiB out
-    int16_t* src = (int16_t*)aligned_alloc(64, total * 2); int32_t* dst = (int32_t*)aligned_alloc(64, total * 4);
-    memset(src, 1, total * 2); memset(dst, 0, total * 4);
+    // ---- early destruction: fewer tiles published than announced, and none at all; must join, not hang
+    for (int published = 0; published < 3; ++published) {
+        std::vector<int32_t> table(64 * 10, 0);
+        std::vector<int16_t> stage(64 * 10, 5);
+        rti::Wideners w(4, 5, 10, 64, table.data());
+        for (int k = 0; k < published; ++k) w.publish({stage.data(), 0, 64, false});
+        if (published) w.wait_done(published);
+    }
+    printf("check ok\n");
+    return 0;
+}
+
+int main(int argc, char **argv) {
+    if (argc > 1 && !strcmp(argv[1], "--check")) return check();
+    const int T = argc > 1 ? atoi(argv[1]) : 8;
+    const size_t total = (size_t)1 << 30;     // elements: 2 GiB in, 4 GiB out
+    int16_t *src = (int16_t *)aligned_alloc(64, total * 2);
+    int32_t *dst = (int32_t *)aligned_alloc(64, total * 4);
+    memset(src, 1, total * 2);
+    memset(dst, 0, total * 4);
     for (int rep = 0; rep < 3; ++rep) {
-        auto t0 = std::chrono::steady_clock::now();
+        const auto t0 = std::chrono::steady_clock::now();
         std::vector<std::thread> th;
-        for (int j = 0; j < T; ++j) th.emplace_back([=] { size_t a = total * j / T, b = total * (j + 1) / T; rti::widen_i16_to_i32(src + a, dst + a, b - a); rti::widen_fence(); });
-        for (auto& x : th) x.join();
-        double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        for (int j = 0; j < T; ++j)
+            th.emplace_back([=] {
+                const size_t a = total * j / T, b = total * (j + 1) / T;
+                rti::widen_i16_to_i32(src + a, dst + a, b - a);
+                rti::widen_fence();
+            });
+        for (auto &x : th) x.join();
+        const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
         printf("T=%d: %.3f s, %.1f GB/s written\n", T, dt, total * 4 / dt / 1e9);
     }
+    return 0;
 }
