@@ -319,8 +319,10 @@ int rti_roi_extract(const uint8_t *d_bgr, int64_t frame_stride, int n_frames, in
  * fits; a tile with a value outside int16 is copied again as int32) into a pinned staging
  * ring, and host threads sign-extend it into h_table while the next tile is in flight:
  * same table, half the PCIe bytes, and h_table need not be pinned.
- * RTI_HOST_TRANSFER=wide|narrow forces either form, RTI_HOST_THREADS the thread count
- * (default: the affinity mask / LOCAL_WORLD_SIZE, at most 16). */
+ * RTI_HOST_TRANSFER=wide|narrow forces either form (mixed: int16, but a tile goes as int32
+ * straight into a pinned h_table when the staging ring is full; measured slower on a
+ * 16-core host), RTI_HOST_THREADS the thread count (default: the affinity mask /
+ * LOCAL_WORLD_SIZE, at most 16). */
 int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cams, int n,
                          int rows_total, int cols, int row0, int rows,
                          const double *h_axis, int g,

@@ -85,7 +85,7 @@ static int pipe_init(HostPipe &c, int dev) {
         RTI_CUDA(cudaEventCreateWithFlags(&c.ev_h2d[b], cudaEventDisableTiming));
         RTI_CUDA(cudaEventCreateWithFlags(&c.ev_fit[b], cudaEventDisableTiming));
         RTI_CUDA(cudaEventCreateWithFlags(&c.ev_comp[b], cudaEventDisableTiming));
-        RTI_CUDA(cudaEventCreateWithFlags(&c.ev_d2h[b], cudaEventDisableTiming));
+        RTI_CUDA(cudaEventCreateWithFlags(&c.ev_d2h[b], cudaEventDisableTiming | cudaEventBlockingSync));
     }
     // the host thread sleeps in cudaEventSynchronize on these instead of spinning: the cores belong to the wideners
     for (int s = 0; s < N_STAGE; ++s)
@@ -163,11 +163,18 @@ static int widen_threads() {
 // (With several ranks per host the shared limit is the host's memory path, which the int32 stores of the
 // widening load as much as the DMA writes they replace: measured 91 GB/s of DMA for 8 ranks, ~105 GB/s of
 // widening stores on 16 cores.)
-static bool want_narrow() {
+// "mixed" (opt-in) adds one rule to "narrow": when the staging ring is full, i.e. the wideners are the slower side
+// right now, the tile does not wait for them but goes as int32 straight into the caller's table (if that is
+// pinned).  Measured on a quiet 16-core host it is SLOWER than plain narrow (533-551 ms against 497 ms per step at
+// 1024^2 x 500, a quarter of the tiles as int32): while an int32 tile holds the link for twice as long, nothing
+// new arrives for the wideners and they run dry.  Kept for hosts with few cores.
+enum TransferMode { TRANSFER_WIDE, TRANSFER_NARROW, TRANSFER_MIXED };
+static TransferMode transfer_mode() {
     const char *e = getenv("RTI_HOST_TRANSFER");
-    if (e && e[0] == 'n') return true;
-    if (e && e[0] == 'w') return false;
-    return local_world() == 1 && widen_threads() >= 8;
+    if (e && e[0] == 'n') return TRANSFER_NARROW;
+    if (e && e[0] == 'w') return TRANSFER_WIDE;
+    if (e && e[0] == 'm') return TRANSFER_MIXED;
+    return local_world() == 1 && widen_threads() >= 8 ? TRANSFER_NARROW : TRANSFER_WIDE;
 }
 
 static thread_local int64_t t_last_d2h_bytes = 0;
@@ -214,7 +221,16 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
     const int64_t slab_pixels = (int64_t)rows * cols;
     const int64_t frame_pitch = (int64_t)rows_total * cols;
     const int64_t n_tiles = (rows + tile_rows - 1) / tile_rows;
-    const bool narrow = h_table != nullptr && want_narrow();
+    const TransferMode mode = h_table != nullptr ? transfer_mode() : TRANSFER_WIDE;
+    const bool narrow = mode != TRANSFER_WIDE;
+    bool mixed = false;
+    if (mode == TRANSFER_MIXED) {                    // int32 tiles go straight into h_table: only worth it when pinned
+        cudaPointerAttributes attr;
+        mixed = cudaPointerGetAttributes(&attr, h_table) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+    }
+    const char *env_every = getenv("RTI_HOST_MIX_EVERY");                  // tests: every k-th tile goes as int32
+    const int mix_every = mixed && env_every ? atoi(env_every) : 0;
     const char *env_limit = getenv("RTI_HOST_NARROW_LIMIT");              // tests lower it to force the int32 re-copy
     const int limit = env_limit && atoi(env_limit) > 0 && atoi(env_limit) < 32767 ? atoi(env_limit) : 32767;
 
@@ -256,11 +272,20 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
         }
         // a staged tile is handed to the wideners one iteration after it was queued, so the GPU always has the
         // next tile's copies queued behind the one the host waits for
+        std::vector<int> slot_of((size_t)n_tiles, -1);       // staging slot of a tile; -1: it went as int32
+        int64_t slot_last[N_STAGE];                          // the tile that used a slot last
+        for (int s = 0; s < N_STAGE; ++s) slot_last[s] = -1;
+        int next_slot = 0;
         auto hand_over = [&](int64_t k) -> int {
-            const int b = (int)(k & 1), sb = (int)(k % N_STAGE);
+            const int b = (int)(k & 1), sb = slot_of[(size_t)k];
             const int r = (int)(k * tile_rows);
             const int tr = (rows - r < tile_rows) ? rows - r : tile_rows;
             const int64_t tp = (int64_t)tr * cols, pix_off = (int64_t)r * cols;
+            if (sb < 0) {                                    // nothing to widen; keeps the tile count in step.  The wait
+                RTI_CUDA(cudaEventSynchronize(c.ev_d2h[b])); // keeps this thread one tile ahead of the copies, no more,
+                wide->publish({nullptr, pix_off, tp, true}); // so the next tile's choice sees how far the wideners are
+                return RTI_OK;
+            }
             RTI_CUDA(cudaEventSynchronize(c.ev_stage[sb]));
             const bool over = c.h_flag[sb] != 0;
             if (over) {            // a value outside int16: this tile again, as int32 (its device tile is still intact)
@@ -274,11 +299,16 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
             return RTI_OK;
         };
         for (int64_t t = 0; t < n_tiles; ++t) {
-            const int b = (int)(t & 1), sb = (int)(t % N_STAGE);
+            const int b = (int)(t & 1), sb = next_slot;
             const int r = (int)(t * tile_rows);
             const int tr = (rows - r < tile_rows) ? rows - r : tile_rows;
             const int64_t tp = (int64_t)tr * cols;
             const int64_t pix_off = (int64_t)r * cols;                    // within the slab
+            bool as_int16 = narrow;
+            if (mixed) {
+                if (mix_every > 0) as_int16 = t % mix_every != mix_every - 1;
+                else as_int16 = slot_last[sb] < 0 || wide->done() > slot_last[sb];   // ring full: do not wait, go wide
+            }
             // ---- H2D: n rows of tp bytes, host pitch = one full frame
             if (t >= 2) RTI_CUDA(cudaStreamWaitEvent(c.s_h2d, c.ev_fit[b], 0));   // frames[b] free again
             RTI_CUDA(cudaMemcpy2DAsync(c.d_frames[b], (size_t)tile_pixels,
@@ -297,7 +327,7 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
             }
             if (rc != RTI_OK) return rc;
             RTI_CUDA(cudaEventRecord(c.ev_fit[b], c.s_comp));
-            if (narrow) {
+            if (as_int16) {
                 RTI_CUDA(cudaMemsetAsync(c.d_flag + b, 0, sizeof(int32_t), c.s_comp));
                 if ((rc = launch_narrow(c.d_table[b], tile_pixels, tp, gg, limit, c.d_narrow[b], c.d_flag + b, c.s_comp)) != RTI_OK)
                     return rc;
@@ -305,8 +335,11 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
             RTI_CUDA(cudaEventRecord(c.ev_comp[b], c.s_comp));
             // ---- D2H
             RTI_CUDA(cudaStreamWaitEvent(c.s_d2h, c.ev_comp[b], 0));
-            if (narrow) {
-                wide->wait_done(t - N_STAGE + 1);                         // staging tile sb has been widened
+            if (as_int16) {
+                wide->wait_done(slot_last[sb] + 1);                       // staging tile sb has been widened
+                slot_of[(size_t)t] = sb;
+                slot_last[sb] = t;
+                next_slot = (sb + 1) % N_STAGE;
                 RTI_CUDA(cudaMemcpyAsync(c.h_stage + (size_t)sb * stage_elems, c.d_narrow[b],
                                          (size_t)gg * tp * sizeof(int16_t), cudaMemcpyDeviceToHost, c.s_d2h));
                 RTI_CUDA(cudaMemcpyAsync(c.h_flag + sb, c.d_flag + b, sizeof(int32_t), cudaMemcpyDeviceToHost, c.s_d2h));
@@ -324,10 +357,8 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
                 d2h_bytes += 6 * tp * (int64_t)sizeof(double);
             }
             RTI_CUDA(cudaEventRecord(c.ev_d2h[b], c.s_d2h));
-            if (narrow) {
-                RTI_CUDA(cudaEventRecord(c.ev_stage[sb], c.s_d2h));
-                if (t >= 1 && (rc = hand_over(t - 1)) != RTI_OK) return rc;
-            }
+            if (as_int16) RTI_CUDA(cudaEventRecord(c.ev_stage[sb], c.s_d2h));
+            if (narrow && t >= 1 && (rc = hand_over(t - 1)) != RTI_OK) return rc;
         }
         if (narrow) {
             if ((rc = hand_over(n_tiles - 1)) != RTI_OK) return rc;

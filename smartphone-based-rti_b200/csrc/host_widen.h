@@ -47,6 +47,10 @@ public:
         std::unique_lock<std::mutex> lk(m_);
         cv_.wait(lk, [&] { return done_ >= tiles; });
     }
+    int64_t done() {                                     // tiles finished so far
+        std::lock_guard<std::mutex> lk(m_);
+        return done_;
+    }
 
 private:
     void stop() {

@@ -478,6 +478,9 @@ def test_compute_from_storage_writes_reference_pickle(torch_cuda, ref_small, mon
     ("narrow", None, None, True),        # int16 over PCIe + host widening threads
     ("narrow", None, "3", False),        # pageable destination, image ranges that do not divide evenly
     ("narrow", "100", "2", True),        # most tiles hold a value beyond the (lowered) limit: int32 re-copy
+    ("mixed2", None, "2", True),         # every second tile goes as int32 straight into the table, the rest as int16
+    ("mixed", None, None, True),         # int16 unless the staging ring is full at that moment
+    ("mixed", None, "1", False),         # pageable destination: never int32 tiles
     (None, None, None, True),            # the library's own choice for this host
 ])
 def test_host_pipeline_tiles_match_single_shot(torch_cuda, monkeypatch, transfer, limit, threads, pinned):
@@ -485,7 +488,11 @@ def test_host_pipeline_tiles_match_single_shot(torch_cuda, monkeypatch, transfer
     forms (the table that reaches the host is the same int32 table either way)."""
     from rti_b200 import _capi, synthetic
     torch = torch_cuda
-    for name, val in (("RTI_HOST_TRANSFER", transfer), ("RTI_HOST_NARROW_LIMIT", limit), ("RTI_HOST_THREADS", threads)):
+    mix_every = None
+    if transfer == "mixed2":
+        transfer, mix_every = "mixed", "2"
+    for name, val in (("RTI_HOST_TRANSFER", transfer), ("RTI_HOST_NARROW_LIMIT", limit), ("RTI_HOST_THREADS", threads),
+                      ("RTI_HOST_MIX_EVERY", mix_every)):
         if val is None:
             monkeypatch.delenv(name, raising=False)
         else:
@@ -517,8 +524,10 @@ def test_host_pipeline_tiles_match_single_shot(torch_cuda, monkeypatch, transfer
         wide_bytes = 4 * g * g * p + 48 * p
         if transfer == "wide":
             assert moved == wide_bytes
-        elif transfer == "narrow" and limit is None:
+        elif transfer == "narrow" and limit is None or transfer == "mixed" and not pinned:
             assert moved == 2 * g * g * p + 48 * p
+        elif mix_every is not None and tile_rows == 3:
+            assert 2 * g * g * p + 48 * p < moved < wide_bytes                 # some of the four tiles each way
     _capi.call("rti_destroy")
 
 

@@ -28,7 +28,7 @@ def main():
     ap.add_argument("--n", type=int, default=500)
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--out", default=None)
-    ap.add_argument("--modes", default="wide,narrow:16,narrow:8,narrow:12,auto,narrow:16:pageable")
+    ap.add_argument("--modes", default="wide,narrow:16,mixed:16,mixed:12,auto,narrow:16:pageable")
     args = ap.parse_args()
     torch.cuda.set_device(0)
     lib = _capi.load()
