@@ -786,8 +786,9 @@ def run_gpu(args, rank, local_rank, world):
                    "d2h_bytes_per_step": d2h_bytes, "ms_per_step": dt * 1e3, "steps": args.e2e_steps,
                    "table_bytes_delivered_per_step": int(table_bytes),
                    "transfer": "int32 over PCIe" if d2h_bytes >= table_bytes else
-                   "%.0f %% of the table as int16 over PCIe, widened to int32 by host threads; the rest as int32 "
-                   "while the staging ring was full" % (100.0 * (table_bytes - d2h_bytes) / (table_bytes / 2)),
+                   "int16 over PCIe, widened to int32 by host threads" if d2h_bytes <= table_bytes // 2 else
+                   "%.0f %% of the table as int16 over PCIe, widened to int32 by host threads; the rest as int32"
+                   % (100.0 * (table_bytes - d2h_bytes) / (table_bytes / 2)),
                    "api": "rti_ptm_compute_host (pinned host frames -> int32 table in pinned host memory)"}
             lib.rti_destroy()
             # the host table of the last e2e step against the oracle (the host call numbers rows from 0)
