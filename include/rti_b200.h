@@ -327,7 +327,17 @@ int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cams, int n,
                          int rows_total, int cols, int row0, int rows,
                          const double *h_axis, int g,
                          int32_t *h_table, double *h_coef, int tile_rows);
-/* bytes the calling thread's last rti_ptm_compute_host moved device -> host (bench.py's
+/* One tile of a DEVICE table into a HOST table through the same staging ring and host threads
+ * (what prepare_images_data, analysis.py:375-411, needs for any interpolation mode):
+ * d_tile int32 [n_images][image_stride], of which tile_pixels per image are used, goes to
+ * h_table[i * host_image_stride + pix_off + x] (pinned or pageable).  The copy is ordered behind
+ * `ready_event` (a cudaEvent_t; the producer's completion) or, when that is NULL, behind
+ * everything queued on `stream` so far; it blocks until the data is in h_table.  int16 or
+ * int32 crossing as for rti_ptm_compute_host (int32 when a value of the tile is outside int16). */
+int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_stride, int64_t n_images,
+                           int64_t tile_pixels, int32_t *h_table, int64_t host_image_stride,
+                           int64_t pix_off, void *ready_event, rti_stream_t stream);
+/* bytes the calling thread's last rti_ptm_compute_host / rti_table_tile_to_host moved device -> host (bench.py's
  * e2e.d2h_bytes_per_step: half of the table's size when it crossed as int16) */
 int64_t rti_host_d2h_bytes(void);
 /* release the cached device workspace / streams of rti_ptm_compute_host */

@@ -80,6 +80,7 @@ SIGNATURES = {
     "rti_relight_from_image": (_i, [_p, _l, _i, _p, _p, _p]),
     "rti_roi_extract": (_i, [_p, _l, _i, _i, _i, _i, _i, _i, _i, _i, _p, _l, _p]),
     "rti_ptm_compute_host": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p, _i]),
+    "rti_table_tile_to_host": (_i, [_p, _l, _l, _l, _p, _l, _l, _p, _p]),
     "rti_host_d2h_bytes": (_l, []),
     "rti_destroy": (_i, []),
 }

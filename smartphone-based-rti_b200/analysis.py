@@ -726,10 +726,12 @@ def table_device(res: InterpolationResult, out=None):
     return out
 
 
-def table_tiles(res: InterpolationResult, tile_bytes=None):
+def table_tiles(res: InterpolationResult, tile_bytes=None, with_events=False):
     """Yields (r0, tr, d_tile): rows [r0, r0 + tr) of every image as an int32 (G*G, tr*cols) device
     tensor, produced through two alternating device buffers of at most tile_bytes each; tile t + 1 is
-    being computed while the caller consumes tile t.  Numerical failures raise after the last tile."""
+    being computed while the caller consumes tile t.  Numerical failures raise after the last tile.
+    with_events: a fourth item, the CUDA event recorded behind the tile's kernels (a consumer on another
+    stream waits for that instead of for the next tile, which is already queued behind it)."""
     torch = _torch()
     g = res.axis.size
     gg = g * g
@@ -756,14 +758,21 @@ def table_tiles(res: InterpolationResult, tile_bytes=None):
         r0, tr = tiles[t]
         view = bufs[t % nbuf][:gg * tr * res.cols].view(gg, tr * res.cols)
         _table_rows(res, r0, tr, view, bad)
-        return view
+        ev = None
+        if with_events:
+            ev = torch.cuda.Event()
+            ev.record()
+        return view, ev
 
     nxt = issue(0)
     for t, (r0, tr) in enumerate(tiles):
-        cur = nxt
+        cur, ev = nxt
         if t + 1 < len(tiles):
             nxt = issue(t + 1)             # its buffer was consumed (synchronously) two tiles ago
-        yield r0, tr, cur
+        if with_events:
+            yield r0, tr, cur, ev
+        else:
+            yield r0, tr, cur
     _raise_if_bad_table(bad)
 
 
@@ -825,10 +834,20 @@ def _table_to_host(d_table):
 
 
 def _table_to_host_tiled(res):
-    """The whole (G*G, P) table as a fresh host ndarray, evaluated in row tiles on the device."""
+    """The whole (G*G, P) table as a fresh host ndarray, evaluated in row tiles on the device.  Each tile
+    leaves through rti_table_tile_to_host (int16 over PCIe when its values fit, a pinned staging ring and
+    host threads that write the int32 result); RTI_TABLE_TO_HOST=python keeps the earlier
+    route (int32 chunks through a pinned ring, copied out by a Python thread pool) for comparison."""
     from concurrent.futures import ThreadPoolExecutor
     gg = res.axis.size ** 2
     out = np.empty((gg, res.rows, res.cols), dtype=np.int32)
+    if os.environ.get("RTI_TABLE_TO_HOST", "native") != "python":
+        torch = _torch()
+        p = res.rows * res.cols
+        for r0, tr, d_tile, ev in table_tiles(res, with_events=True):
+            _capi.call("rti_table_tile_to_host", d_tile.data_ptr(), tr * res.cols, gg, tr * res.cols,
+                       out.ctypes.data, p, r0 * res.cols, ev.cuda_event, _stream_ptr(torch))
+        return out.reshape(gg, p)
     threads = max(1, min(8, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else 4))
     with ThreadPoolExecutor(threads) as pool:
         for r0, tr, d_tile in table_tiles(res):

@@ -37,7 +37,8 @@ struct HostPipe {
     int16_t *h_stage = nullptr;         // pinned, N_STAGE tiles
     int32_t *h_flag = nullptr;          // pinned [N_STAGE]
     cudaEvent_t ev_stage[N_STAGE] = {};
-    size_t narrow_bytes = 0, stage_bytes = 0;
+    int16_t *d_narrow_tile = nullptr;   // rti_table_tile_to_host: the whole tile narrowed
+    size_t narrow_bytes = 0, narrow_tile_bytes = 0, stage_bytes = 0;
     bool ready = false;
 };
 
@@ -66,7 +67,7 @@ static int pipe_release(HostPipe &c) {
         cudaEventDestroy(c.ev_comp[b]); cudaEventDestroy(c.ev_d2h[b]);
     }
     cudaFree(c.d_cams); cudaFree(c.d_axis); cudaFree(c.d_bad);
-    cudaFree(c.d_narrow[0]); cudaFree(c.d_narrow[1]); cudaFree(c.d_flag);
+    cudaFree(c.d_narrow[0]); cudaFree(c.d_narrow[1]); cudaFree(c.d_narrow_tile); cudaFree(c.d_flag);
     if (c.h_stage) cudaFreeHost(c.h_stage);
     if (c.h_flag) cudaFreeHost(c.h_flag);
     for (int s = 0; s < N_STAGE; ++s) cudaEventDestroy(c.ev_stage[s]);
@@ -263,7 +264,7 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
         std::unique_ptr<Wideners> wide;
         if (narrow) {
             try {
-                wide.reset(new Wideners(widen_threads(), n_tiles, gg, slab_pixels, h_table));
+                wide.reset(new Wideners(widen_threads(), n_tiles, slab_pixels, h_table));
             } catch (const std::exception &e) {           // no threads to be had: say so instead of terminating
                 set_error("rti_ptm_compute_host: cannot start the widening threads (%s); RTI_HOST_TRANSFER=wide avoids them",
                           e.what());
@@ -283,7 +284,7 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
             const int64_t tp = (int64_t)tr * cols, pix_off = (int64_t)r * cols;
             if (sb < 0) {                                    // nothing to widen; keeps the tile count in step.  The wait
                 RTI_CUDA(cudaEventSynchronize(c.ev_d2h[b])); // keeps this thread one tile ahead of the copies, no more,
-                wide->publish({nullptr, pix_off, tp, true}); // so the next tile's choice sees how far the wideners are
+                wide->publish({nullptr, 0, gg, pix_off, tp, Wideners::SKIP});   // so the next tile's choice sees the wideners
                 return RTI_OK;
             }
             RTI_CUDA(cudaEventSynchronize(c.ev_stage[sb]));
@@ -295,7 +296,7 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
                 RTI_CUDA(cudaStreamSynchronize(c.s_d2h));
                 d2h_bytes += gg * tp * (int64_t)sizeof(int32_t);
             }
-            wide->publish({c.h_stage + (size_t)sb * stage_elems, pix_off, tp, over});
+            wide->publish({c.h_stage + (size_t)sb * stage_elems, 0, gg, pix_off, tp, over ? Wideners::SKIP : Wideners::I16});
             return RTI_OK;
         };
         for (int64_t t = 0; t < n_tiles; ++t) {
@@ -379,6 +380,94 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
         set_error("rti_ptm_compute_host: table values not representable as int32 (NaN/inf/overflow)");
         return RTI_ERR_NONFINITE;
     }
+    return RTI_OK;
+}
+
+
+// One device table tile -> the caller's host table through the same staging ring and host threads, in chunks
+// of whole images: the D2H copy of chunk c + 1 runs while chunk c is widened (int16 crossing) or copied
+// (int32 crossing: wide mode, or a value of the tile is outside int16).
+extern "C" int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_stride, int64_t n_images, int64_t tile_pixels,
+                                      int32_t *h_table, int64_t host_image_stride, int64_t pix_off, void *ready_event,
+                                      rti_stream_t stream) {
+    RTI_REQUIRE(d_tile && h_table, "rti_table_tile_to_host: NULL pointer");
+    RTI_REQUIRE(n_images > 0 && tile_pixels > 0 && image_stride >= tile_pixels && pix_off >= 0 &&
+                host_image_stride >= pix_off + tile_pixels, "rti_table_tile_to_host: bad shape");
+    int dev = 0;
+    RTI_CUDA(cudaGetDevice(&dev));
+    RTI_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "rti_table_tile_to_host: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_pipe_mutex[dev]);
+    HostPipe &c = g_pipes[dev];
+    int rc = pipe_init(c, dev);
+    if (rc != RTI_OK) return rc;
+    // order behind the producer of the tile: the caller's event, or everything queued on its stream so far
+    if (ready_event != nullptr) {
+        RTI_CUDA(cudaStreamWaitEvent(c.s_d2h, static_cast<cudaEvent_t>(ready_event), 0));
+    } else {
+        RTI_CUDA(cudaEventRecord(c.ev_comp[0], as_stream(stream)));
+        RTI_CUDA(cudaStreamWaitEvent(c.s_d2h, c.ev_comp[0], 0));
+    }
+    bool narrow = transfer_mode() != TRANSFER_WIDE;
+    const char *env_limit = getenv("RTI_HOST_NARROW_LIMIT");
+    const int limit = env_limit && atoi(env_limit) > 0 && atoi(env_limit) < 32767 ? atoi(env_limit) : 32767;
+    if (narrow) {
+        if ((rc = grow((void **)&c.d_narrow_tile, &c.narrow_tile_bytes, (size_t)n_images * tile_pixels * sizeof(int16_t))) != RTI_OK)
+            return rc;
+        RTI_CUDA(cudaMemsetAsync(c.d_flag, 0, sizeof(int32_t), c.s_d2h));
+        if ((rc = launch_narrow(d_tile, image_stride, tile_pixels, n_images, limit, c.d_narrow_tile, c.d_flag, c.s_d2h)) != RTI_OK)
+            return rc;
+        RTI_CUDA(cudaMemcpyAsync(c.h_flag, c.d_flag, sizeof(int32_t), cudaMemcpyDeviceToHost, c.s_d2h));
+        RTI_CUDA(cudaStreamSynchronize(c.s_d2h));
+        if (c.h_flag[0] != 0) narrow = false;                 // a value outside int16: this tile crosses as int32
+    }
+    const size_t esize = narrow ? sizeof(int16_t) : sizeof(int32_t);
+    const size_t chunk_bytes = (size_t)64 << 20;
+    int64_t per = (int64_t)(chunk_bytes / ((size_t)tile_pixels * esize));
+    per = per < 1 ? 1 : (per > n_images ? n_images : per);
+    const size_t slot_bytes = (size_t)per * tile_pixels * esize;
+    if (c.stage_bytes < N_STAGE * slot_bytes) {
+        if (c.h_stage) RTI_CUDA(cudaFreeHost(c.h_stage));
+        c.h_stage = nullptr;
+        c.stage_bytes = 0;
+        const size_t want = N_STAGE * (slot_bytes > chunk_bytes ? slot_bytes : chunk_bytes);
+        RTI_CUDA(cudaHostAlloc(&c.h_stage, want, cudaHostAllocDefault));
+        c.stage_bytes = want;
+    }
+    const int64_t n_chunks = (n_images + per - 1) / per;
+    int64_t d2h_bytes = 0;
+    {
+        std::unique_ptr<Wideners> wide;
+        try {
+            wide.reset(new Wideners(widen_threads(), n_chunks, host_image_stride, h_table));
+        } catch (const std::exception &e) {
+            set_error("rti_table_tile_to_host: cannot start the host threads (%s)", e.what());
+            return RTI_ERR_ARG;
+        }
+        auto slot = [&](int64_t k) { return reinterpret_cast<unsigned char *>(c.h_stage) + (size_t)(k % N_STAGE) * slot_bytes; };
+        auto hand_over = [&](int64_t k) -> int {
+            const int64_t i0 = k * per, cnt = (n_images - i0 < per) ? n_images - i0 : per;
+            RTI_CUDA(cudaEventSynchronize(c.ev_stage[k % N_STAGE]));
+            wide->publish({slot(k), i0, cnt, pix_off, tile_pixels, narrow ? Wideners::I16 : Wideners::I32});
+            return RTI_OK;
+        };
+        for (int64_t k = 0; k < n_chunks; ++k) {
+            const int64_t i0 = k * per, cnt = (n_images - i0 < per) ? n_images - i0 : per;
+            wide->wait_done(k - N_STAGE + 1);                 // the slot's previous chunk is in the table
+            if (narrow)
+                RTI_CUDA(cudaMemcpyAsync(slot(k), c.d_narrow_tile + i0 * tile_pixels, (size_t)cnt * tile_pixels * esize,
+                                         cudaMemcpyDeviceToHost, c.s_d2h));
+            else
+                RTI_CUDA(cudaMemcpy2DAsync(slot(k), (size_t)tile_pixels * esize, d_tile + i0 * image_stride,
+                                           (size_t)image_stride * esize, (size_t)tile_pixels * esize, (size_t)cnt,
+                                           cudaMemcpyDeviceToHost, c.s_d2h));
+            d2h_bytes += cnt * tile_pixels * (int64_t)esize;
+            RTI_CUDA(cudaEventRecord(c.ev_stage[k % N_STAGE], c.s_d2h));
+            if (k >= 1 && (rc = hand_over(k - 1)) != RTI_OK) return rc;
+        }
+        if ((rc = hand_over(n_chunks - 1)) != RTI_OK) return rc;
+        wide->wait_done(n_chunks);
+    }
+    t_last_d2h_bytes = d2h_bytes;
     return RTI_OK;
 }
 

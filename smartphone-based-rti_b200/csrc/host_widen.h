@@ -5,6 +5,7 @@
 #include <mutex>
 #include <stddef.h>
 #include <stdint.h>
+#include <string.h>
 #include <thread>
 #include <vector>
 
@@ -15,15 +16,17 @@ void widen_i16_to_i32(const int16_t *src, int32_t *dst, size_t n);
 // orders the calling thread's non-temporal stores before whatever it publishes next
 void widen_fence();
 
-// Host threads that widen staged int16 tiles into the caller's int32 table, tile by tile in the order they
-// are published.  A tile is `gg` images of `tp` values each, packed [gg][tp]; image i goes to
-// h_table + i * slab_pixels + pix_off.  Thread j owns images [gg j / T, gg (j + 1) / T) of every tile.
-// The destructor stops and joins the threads, so an early error return of the caller cannot leave any behind.
+// Host threads that move staged tiles into the caller's int32 table, tile by tile in the order they are
+// published.  A tile is `n_img` images of `tp` values each, packed [n_img][tp] as int16 (widened) or int32
+// (copied); image i of the tile goes to h_table + (img0 + i) * slab_pixels + pix_off.  Thread j owns images
+// [n_img j / T, n_img (j + 1) / T) of every tile.  The destructor stops and joins the threads, so an early
+// error return of the caller cannot leave any behind.
 class Wideners {
 public:
-    struct Job { const int16_t *src; int64_t pix_off, tp; bool skip; };
-    Wideners(int threads, int64_t n_tiles, int64_t gg, int64_t slab_pixels, int32_t *h_table)
-        : jobs_((size_t)n_tiles), left_((size_t)n_tiles, threads), n_tiles_(n_tiles), gg_(gg),
+    enum Kind { SKIP = 0, I16 = 1, I32 = 2 };
+    struct Job { const void *src; int64_t img0, n_img, pix_off, tp; Kind kind; };
+    Wideners(int threads, int64_t n_tiles, int64_t slab_pixels, int32_t *h_table)
+        : jobs_((size_t)n_tiles), left_((size_t)n_tiles, threads), n_tiles_(n_tiles),
           slab_pixels_(slab_pixels), h_table_(h_table), threads_(threads) {
         try {
             for (int j = 0; j < threads; ++j) th_.emplace_back([this, j] { run(j); });
@@ -63,7 +66,6 @@ private:
         th_.clear();
     }
     void run(int j) {
-        const int64_t i0 = gg_ * j / threads_, i1 = gg_ * (j + 1) / threads_;
         for (int64_t k = 0; k < n_tiles_; ++k) {
             Job job;
             {
@@ -72,9 +74,15 @@ private:
                 if (published_ <= k) return;             // stopped before this tile arrived
                 job = jobs_[(size_t)k];
             }
-            if (!job.skip) {
-                for (int64_t i = i0; i < i1; ++i)
-                    widen_i16_to_i32(job.src + i * job.tp, h_table_ + i * slab_pixels_ + job.pix_off, (size_t)job.tp);
+            if (job.kind != SKIP) {
+                const int64_t i0 = job.n_img * j / threads_, i1 = job.n_img * (j + 1) / threads_;
+                for (int64_t i = i0; i < i1; ++i) {
+                    int32_t *dst = h_table_ + (job.img0 + i) * slab_pixels_ + job.pix_off;
+                    if (job.kind == I16)
+                        widen_i16_to_i32(static_cast<const int16_t *>(job.src) + i * job.tp, dst, (size_t)job.tp);
+                    else
+                        memcpy(dst, static_cast<const int32_t *>(job.src) + i * job.tp, (size_t)job.tp * sizeof(int32_t));
+                }
                 widen_fence();
             }
             bool last;
@@ -91,7 +99,7 @@ private:
     std::vector<int> left_;
     std::mutex m_;
     std::condition_variable cv_;
-    int64_t published_ = 0, done_ = 0, n_tiles_, gg_, slab_pixels_;
+    int64_t published_ = 0, done_ = 0, n_tiles_, slab_pixels_;
     int32_t *h_table_;
     int threads_;
     bool abort_ = false;

@@ -531,6 +531,46 @@ def test_host_pipeline_tiles_match_single_shot(torch_cuda, monkeypatch, transfer
     _capi.call("rti_destroy")
 
 
+@pytest.mark.parametrize("transfer,limit,threads,pinned", [
+    ("wide", None, "2", False), ("narrow", None, "3", False), ("narrow", None, None, True),
+    ("narrow", "50", "2", False), (None, None, None, False),
+])
+def test_table_tile_to_host_every_crossing(torch_cuda, monkeypatch, transfer, limit, threads, pinned):
+    """rti_table_tile_to_host: a strided device tile lands in its place inside a larger host table, bit for bit,
+    as int16 or int32 over PCIe, through one or many staging chunks, ordered by an event or by the stream."""
+    from rti_b200 import _capi
+    torch = torch_cuda
+    for name, val in (("RTI_HOST_TRANSFER", transfer), ("RTI_HOST_NARROW_LIMIT", limit), ("RTI_HOST_THREADS", threads)):
+        if val is None:
+            monkeypatch.delenv(name, raising=False)
+        else:
+            monkeypatch.setenv(name, val)
+    rng = np.random.default_rng(5)
+    for n_images, tp, stride, host_stride, pix_off, hi in ((7, 37, 41, 100, 13, 300), (400, 108, 108, 540, 432, 300),
+                                                          (3, 16, 16, 16, 0, 40000), (70000, 263, 264, 263, 0, 120)):
+        tile = rng.integers(-hi, hi, (n_images, stride)).astype(np.int32)
+        d_tile = torch.from_numpy(tile).cuda()
+        host = torch.full((n_images, host_stride), -7, dtype=torch.int32)
+        if pinned:
+            host = host.pin_memory()
+        ev = torch.cuda.Event()
+        ev.record()
+        for ready in (ev.cuda_event, None):
+            host.fill_(-7)
+            _capi.call("rti_table_tile_to_host", d_tile.data_ptr(), stride, n_images, tp, host.data_ptr(), host_stride,
+                       pix_off, ready, torch.cuda.current_stream().cuda_stream)
+            want = np.full((n_images, host_stride), -7, dtype=np.int32)
+            want[:, pix_off:pix_off + tp] = tile[:, :tp]
+            assert np.array_equal(host.numpy(), want)
+            moved = _capi.load().rti_host_d2h_bytes()
+            fits = hi <= 32768 and (limit is None or hi <= int(limit))
+            if transfer == "narrow":
+                assert moved == n_images * tp * (2 if fits else 4)
+            elif transfer == "wide":
+                assert moved == n_images * tp * 4
+    _capi.call("rti_destroy")
+
+
 def _fit_soa(torch, lx, ly, inten):
     from rti_b200 import _capi
     p, n = lx.shape

@@ -38,20 +38,25 @@ static int check() {
         std::vector<int32_t> table((size_t)(gg * slab), -7), ref((size_t)(gg * slab), -7);
         int64_t tp_max = 0;
         for (auto v : tp) tp_max = v > tp_max ? v : tp_max;
-        std::vector<int16_t> stage((size_t)(3 * gg * tp_max));
+        std::vector<int32_t> stage((size_t)(3 * gg * tp_max));            // holds int16 or int32 tiles
         {
-            rti::Wideners w(threads, n_tiles, gg, slab, table.data());
+            rti::Wideners w(threads, n_tiles, slab, table.data());
             for (int64_t k = 0; k < n_tiles; ++k) {
                 w.wait_done(k - 2);                                        // staging buffer k % 3 is free again
-                int16_t *buf = stage.data() + (size_t)((k % 3) * gg * tp_max);
-                const bool skip = rng() % 4 == 0;
-                for (int64_t i = 0; i < gg; ++i)
+                int32_t *buf32 = stage.data() + (size_t)((k % 3) * gg * tp_max);
+                int16_t *buf16 = reinterpret_cast<int16_t *>(buf32);
+                const rti::Wideners::Kind kind = (rti::Wideners::Kind)(rng() % 3);      // skipped, int16 or int32
+                // a tile may also cover only a range of the images (the chunks of rti_table_tile_to_host)
+                const int64_t img0 = rng() % 2 ? 0 : (int64_t)(rng() % (uint64_t)gg);
+                const int64_t n_img = img0 ? gg - img0 : gg;
+                for (int64_t i = 0; i < n_img; ++i)
                     for (int64_t x = 0; x < tp[(size_t)k]; ++x) {
-                        const int16_t v = (int16_t)(rng() & 0xffff);
-                        buf[i * tp[(size_t)k] + x] = v;
-                        if (!skip) ref[(size_t)(i * slab + off[(size_t)k] + x)] = v;
+                        const int32_t v = kind == rti::Wideners::I32 ? (int32_t)rng() : (int32_t)(int16_t)(rng() & 0xffff);
+                        if (kind == rti::Wideners::I32) buf32[i * tp[(size_t)k] + x] = v;
+                        else buf16[i * tp[(size_t)k] + x] = (int16_t)v;
+                        if (kind != rti::Wideners::SKIP) ref[(size_t)((img0 + i) * slab + off[(size_t)k] + x)] = v;
                     }
-                w.publish({buf, off[(size_t)k], tp[(size_t)k], skip});
+                w.publish({buf32, img0, n_img, off[(size_t)k], tp[(size_t)k], kind});
             }
             w.wait_done(n_tiles);
         }
@@ -61,8 +66,8 @@ static int check() {
     for (int published = 0; published < 3; ++published) {
         std::vector<int32_t> table(64 * 10, 0);
         std::vector<int16_t> stage(64 * 10, 5);
-        rti::Wideners w(4, 5, 10, 64, table.data());
-        for (int k = 0; k < published; ++k) w.publish({stage.data(), 0, 64, false});
+        rti::Wideners w(4, 5, 64, table.data());
+        for (int k = 0; k < published; ++k) w.publish({stage.data(), 0, 10, 0, 64, rti::Wideners::I16});
         if (published) w.wait_done(published);
     }
     printf("check ok\n");
