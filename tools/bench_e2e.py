@@ -46,8 +46,11 @@ def main():
     first = None
     for mode in args.modes.split(","):
         parts = mode.split(":")
-        for name in ("RTI_HOST_TRANSFER", "RTI_HOST_THREADS"):
+        for name in ("RTI_HOST_TRANSFER", "RTI_HOST_THREADS", "RTI_HOST_MIX_EVERY"):
             os.environ.pop(name, None)
+        for x in parts[2:]:
+            if x.startswith("mix"):                               # mixed:16:mix8 = every 8th tile as int32
+                os.environ["RTI_HOST_MIX_EVERY"] = x[3:]
         if parts[0] != "auto":
             os.environ["RTI_HOST_TRANSFER"] = parts[0]
         if len(parts) > 1:
