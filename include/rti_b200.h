@@ -340,6 +340,17 @@ int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_stride, int64_t 
 /* bytes the calling thread's last rti_ptm_compute_host / rti_table_tile_to_host moved device -> host (bench.py's
  * e2e.d2h_bytes_per_step: half of the table's size when it crossed as int16) */
 int64_t rti_host_d2h_bytes(void);
+/* ---- frame-list ingest helpers (host only, no CUDA) -----------------------------------
+ * ut.read_from_file (Utils/utilities.py:84-96) decodes '<name>.pbz2' with one thread; ingest.py
+ * decodes the file's bzip2 blocks in parallel and uses these two byte loops for what would
+ * otherwise stay serial Python: finding the 48-bit block magic at any BIT offset (ascending bit
+ * offsets into bit_offsets[0, cap); the return value is the number found, which may exceed cap;
+ * threads <= 0: one per core) and copying a bit range (MSB first within a byte; returns the
+ * bit offset after the copy; the tail of the last byte is zeroed). */
+int64_t rti_find_magic48(const uint8_t *buf, int64_t n, uint64_t magic48, int64_t *bit_offsets,
+                         int64_t cap, int threads);
+int64_t rti_copy_bits(const uint8_t *src, int64_t src_bit0, int64_t nbits, uint8_t *dst,
+                      int64_t dst_bit0);
 /* release the cached device workspace / streams of rti_ptm_compute_host */
 int rti_destroy(void);
 

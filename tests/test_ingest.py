@@ -138,3 +138,48 @@ def test_gpu_load_frame_stack_feeds_compute(tmp_path, lib):
         assert int(bad.item()) == 0 and np.abs(got - ref).max() <= 1e-9 * np.abs(ref).max()
     finally:
         rti_b200.constants.ROI_DIAMETER = old
+
+
+def test_native_scan_and_bit_copy_equal_the_python_forms():
+    """csrc/host_bz2.cpp (rti_find_magic48, rti_copy_bits) against ingest.py's pure-Python forms: the magic at
+    every bit alignment, at both ends of the buffer, overlapping a thread-chunk seam, in random data; bit
+    ranges at every source / destination alignment."""
+    import ctypes as C
+    from rti_b200 import _capi, ingest
+    lib = _capi.load()
+    rng = np.random.default_rng(3)
+    magic = ingest.BLOCK_MAGIC
+
+    def plant(buf, bit):                       # write the 48-bit magic at an arbitrary bit offset
+        bits = np.unpackbits(buf)
+        bits[bit:bit + 48] = ingest._bits_of(magic, 48)
+        return np.packbits(bits)
+
+    for n, where in ((6, [0]), (7, [3]), (64, [0, 101, 64 * 8 - 48]), (4096, [17, 1000, 4096 * 8 - 49]),
+                     (3 << 20, [5, (1 << 20) * 8 - 20, (1 << 20) * 8 + 43, (2 << 20) * 8 - 1, (3 << 20) * 8 - 48])):
+        buf = rng.integers(0, 256, n, dtype=np.uint8)
+        for bit in where:
+            buf = plant(buf, bit)
+        raw = buf.tobytes()
+        want = ingest._find_magic_bits_py(raw, magic)
+        assert set(where) <= set(want)
+        for threads in (1, 3, 0):
+            out = (C.c_int64 * 64)()
+            cnt = lib.rti_find_magic48(raw, len(raw), magic, out, 64, threads)
+            assert list(out[:cnt]) == want
+        assert ingest._find_magic_bits(raw, magic) == want
+        assert lib.rti_find_magic48(raw, len(raw), magic, None, 0, 1) == len(want)      # count only
+    src = rng.integers(0, 256, 64, dtype=np.uint8)
+    sbits = np.unpackbits(src)
+    for s0 in range(0, 19):
+        for d0 in range(0, 11):
+            for nbits in (1, 5, 8, 13, 64, 200):
+                dst = np.full(48, 0xFF, dtype=np.uint8)
+                end = lib.rti_copy_bits(src.ctypes.data, s0, nbits, dst.ctypes.data, d0)
+                assert end == d0 + nbits
+                want_bits = np.unpackbits(np.full(48, 0xFF, dtype=np.uint8))
+                want_bits[d0:d0 + nbits] = sbits[s0:s0 + nbits]
+                last = (d0 + nbits + 7) // 8
+                want_bits[d0 + nbits:last * 8] = 0                     # the tail of the last byte is zeroed
+                assert np.array_equal(dst[:last], np.packbits(want_bits)[:last]), (s0, d0, nbits)
+                assert np.all(dst[last:] == 0xFF)                      # nothing beyond it is touched
