@@ -337,6 +337,13 @@ int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cams, int n,
 int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_stride, int64_t n_images,
                            int64_t tile_pixels, int32_t *h_table, int64_t host_image_stride,
                            int64_t pix_off, void *ready_event, rti_stream_t stream);
+/* The same into a FILE: image i's values go to byte h_offsets[i] + 4 * pix_off of the open file
+ * descriptor fd, written with pwrite by the host threads -- the image payloads of the result
+ * pickle that ut.write_on_file(.., compressed=False) produces (Utils/utilities.py:48-70,
+ * analysis.py:475), laid out by table_io.TableTileWriter.  h_offsets: host int64 [n_images]. */
+int rti_table_tile_to_file(const int32_t *d_tile, int64_t image_stride, int64_t n_images,
+                           int64_t tile_pixels, int fd, const int64_t *h_offsets, int64_t pix_off,
+                           void *ready_event, rti_stream_t stream);
 /* bytes the calling thread's last rti_ptm_compute_host / rti_table_tile_to_host moved device -> host (bench.py's
  * e2e.d2h_bytes_per_step: half of the table's size when it crossed as int16) */
 int64_t rti_host_d2h_bytes(void);

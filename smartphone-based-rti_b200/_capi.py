@@ -81,6 +81,7 @@ SIGNATURES = {
     "rti_roi_extract": (_i, [_p, _l, _i, _i, _i, _i, _i, _i, _i, _i, _p, _l, _p]),
     "rti_ptm_compute_host": (_i, [_p, _p, _i, _i, _i, _i, _i, _p, _i, _p, _p, _i]),
     "rti_table_tile_to_host": (_i, [_p, _l, _l, _l, _p, _l, _l, _p, _p]),
+    "rti_table_tile_to_file": (_i, [_p, _l, _l, _l, _i, _p, _l, _p, _p]),
     "rti_host_d2h_bytes": (_l, []),
     "rti_find_magic48": (_l, [_p, _l, C.c_uint64, _p, _l, _i]),
     "rti_copy_bits": (_l, [_p, _l, _l, _p, _l]),

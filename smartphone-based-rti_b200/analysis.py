@@ -999,18 +999,27 @@ def write_table_file(res, filename):
     writer = table_io.TableTileWriter(g, g, (res.rows, res.cols), np.int32, filename)
     threads = max(1, min(8, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else 4))
     try:
-        with ThreadPoolExecutor(threads) as pool:
-            # row tiles of the ROI: device tile -> pinned ring -> pwrite at each image's fixed offset; the
-            # D2H copy of the next chunk and the evaluation of the next tile run while this chunk is written
-            for r0, tr, d_tile in table_tiles(res):
-                def consume(chunk, i0, r0=r0):
-                    cnt = chunk.shape[0]
-                    step = (cnt + threads - 1) // threads
-                    futs = [pool.submit(writer.write_rows, i0 + a, chunk[a:min(cnt, a + step)], r0)
-                            for a in range(0, cnt, step)]
-                    for f in futs:
-                        f.result()
-                _stream_images(d_tile, consume)
+        if os.environ.get("RTI_TABLE_TO_HOST", "native") != "python":
+            # row tiles of the ROI: device tile -> (int16 over PCIe when it fits) -> pinned ring -> host threads
+            # that pwrite each image's rows at its fixed offset (rti_table_tile_to_file); the evaluation of the
+            # next tile runs meanwhile
+            torch = _torch()
+            offsets = np.ascontiguousarray(writer.offsets, dtype=np.int64)
+            for r0, tr, d_tile, ev in table_tiles(res, with_events=True):
+                _capi.call("rti_table_tile_to_file", d_tile.data_ptr(), tr * res.cols, g * g, tr * res.cols,
+                           writer.fd, offsets.ctypes.data, r0 * res.cols, ev.cuda_event, _stream_ptr(torch))
+        else:
+            # the earlier route: int32 chunks through a pinned ring, pwrite from a Python thread pool
+            with ThreadPoolExecutor(threads) as pool:
+                for r0, tr, d_tile in table_tiles(res):
+                    def consume(chunk, i0, r0=r0):
+                        cnt = chunk.shape[0]
+                        step = (cnt + threads - 1) // threads
+                        futs = [pool.submit(writer.write_rows, i0 + a, chunk[a:min(cnt, a + step)], r0)
+                                for a in range(0, cnt, step)]
+                        for f in futs:
+                            f.result()
+                    _stream_images(d_tile, consume)
     finally:
         writer.close()
     print("Saved file {}".format(filename))

@@ -387,15 +387,13 @@ extern "C" int rti_ptm_compute_host(const uint8_t *h_frames, const double *h_cam
 // One device table tile -> the caller's host table through the same staging ring and host threads, in chunks
 // of whole images: the D2H copy of chunk c + 1 runs while chunk c is widened (int16 crossing) or copied
 // (int32 crossing: wide mode, or a value of the tile is outside int16).
-extern "C" int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_stride, int64_t n_images, int64_t tile_pixels,
-                                      int32_t *h_table, int64_t host_image_stride, int64_t pix_off, void *ready_event,
-                                      rti_stream_t stream) {
-    RTI_REQUIRE(d_tile && h_table, "rti_table_tile_to_host: NULL pointer");
-    RTI_REQUIRE(n_images > 0 && tile_pixels > 0 && image_stride >= tile_pixels && pix_off >= 0 &&
-                host_image_stride >= pix_off + tile_pixels, "rti_table_tile_to_host: bad shape");
+// Destination: rows of a host table (h_table) or of the image payloads of a result file (fd + per-image offsets).
+static int tile_to_sink(const int32_t *d_tile, int64_t image_stride, int64_t n_images, int64_t tile_pixels,
+                        int32_t *h_table, int64_t host_image_stride, int fd, const int64_t *file_offsets,
+                        int64_t pix_off, void *ready_event, rti_stream_t stream) {
     int dev = 0;
     RTI_CUDA(cudaGetDevice(&dev));
-    RTI_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "rti_table_tile_to_host: device ordinal %d out of range", dev);
+    RTI_REQUIRE(dev >= 0 && dev < MAX_DEVICES, "rti_table_tile_to_host/file: device ordinal %d out of range", dev);
     std::lock_guard<std::mutex> lock(g_pipe_mutex[dev]);
     HostPipe &c = g_pipes[dev];
     int rc = pipe_init(c, dev);
@@ -438,7 +436,7 @@ extern "C" int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_strid
     {
         std::unique_ptr<Wideners> wide;
         try {
-            wide.reset(new Wideners(widen_threads(), n_chunks, host_image_stride, h_table));
+            wide.reset(new Wideners(widen_threads(), n_chunks, host_image_stride, h_table, fd, file_offsets));
         } catch (const std::exception &e) {
             set_error("rti_table_tile_to_host: cannot start the host threads (%s)", e.what());
             return RTI_ERR_ARG;
@@ -466,9 +464,35 @@ extern "C" int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_strid
         }
         if ((rc = hand_over(n_chunks - 1)) != RTI_OK) return rc;
         wide->wait_done(n_chunks);
+        if (wide->error() != 0) {
+            set_error("rti_table_tile_to_file: pwrite failed (errno %d)", wide->error());
+            return RTI_ERR_ARG;
+        }
     }
     t_last_d2h_bytes = d2h_bytes;
     return RTI_OK;
+}
+
+extern "C" int rti_table_tile_to_host(const int32_t *d_tile, int64_t image_stride, int64_t n_images, int64_t tile_pixels,
+                                      int32_t *h_table, int64_t host_image_stride, int64_t pix_off, void *ready_event,
+                                      rti_stream_t stream) {
+    RTI_REQUIRE(d_tile && h_table, "rti_table_tile_to_host: NULL pointer");
+    RTI_REQUIRE(n_images > 0 && tile_pixels > 0 && image_stride >= tile_pixels && pix_off >= 0 &&
+                host_image_stride >= pix_off + tile_pixels, "rti_table_tile_to_host: bad shape");
+    return tile_to_sink(d_tile, image_stride, n_images, tile_pixels, h_table, host_image_stride, -1, nullptr, pix_off,
+                        ready_event, stream);
+}
+
+// The same into a file: image i's int32 values go to byte h_offsets[i] + 4 pix_off of the open descriptor `fd`
+// (pwrite from the host threads; the file's image payloads are laid out by table_io.TableTileWriter).
+extern "C" int rti_table_tile_to_file(const int32_t *d_tile, int64_t image_stride, int64_t n_images, int64_t tile_pixels,
+                                      int fd, const int64_t *h_offsets, int64_t pix_off, void *ready_event,
+                                      rti_stream_t stream) {
+    RTI_REQUIRE(d_tile && h_offsets && fd >= 0, "rti_table_tile_to_file: NULL pointer or bad descriptor");
+    RTI_REQUIRE(n_images > 0 && tile_pixels > 0 && image_stride >= tile_pixels && pix_off >= 0,
+                "rti_table_tile_to_file: bad shape");
+    return tile_to_sink(d_tile, image_stride, n_images, tile_pixels, nullptr, 0, fd, h_offsets, pix_off, ready_event,
+                        stream);
 }
 
 extern "C" int rti_destroy(void) {

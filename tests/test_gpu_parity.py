@@ -571,6 +571,44 @@ def test_table_tile_to_host_every_crossing(torch_cuda, monkeypatch, transfer, li
     _capi.call("rti_destroy")
 
 
+@pytest.mark.parametrize("transfer", ["wide", "narrow", None])
+def test_table_tile_to_file_writes_rows_at_their_offsets(torch_cuda, monkeypatch, tmp_path, transfer):
+    """rti_table_tile_to_file: rows of every image land at h_offsets[i] + 4 pix_off of the file and nothing else is
+    touched; a failing descriptor is an error, not a silent success."""
+    import os
+    from rti_b200 import _capi
+    torch = torch_cuda
+    if transfer is None:
+        monkeypatch.delenv("RTI_HOST_TRANSFER", raising=False)
+    else:
+        monkeypatch.setenv("RTI_HOST_TRANSFER", transfer)
+    rng = np.random.default_rng(9)
+    n_images, rows, cols, gap = 300, 7, 36, 13
+    per = rows * cols * 4 + gap
+    offsets = (5 + per * np.arange(n_images)).astype(np.int64)
+    path = str(tmp_path / "t.bin")
+    want = np.full(5 + per * n_images, 0xEE, dtype=np.uint8)
+    fd = os.open(path, os.O_RDWR | os.O_CREAT | os.O_TRUNC, 0o644)
+    try:
+        os.pwrite(fd, want.tobytes(), 0)
+        for r0, tr, hi in ((0, 3, 200), (3, 4, 70000)):                   # second band: values beyond int16
+            tile = rng.integers(-hi, hi, (n_images, tr * cols + 4)).astype(np.int32)      # strided on the device
+            d_tile = torch.from_numpy(tile).cuda()
+            _capi.call("rti_table_tile_to_file", d_tile.data_ptr(), tile.shape[1], n_images, tr * cols, fd,
+                       offsets.ctypes.data, r0 * cols, None, torch.cuda.current_stream().cuda_stream)
+            for i in range(n_images):
+                a = offsets[i] + 4 * r0 * cols
+                want[a:a + 4 * tr * cols] = tile[i, :tr * cols].view(np.uint8)
+        got = np.frombuffer(os.pread(fd, want.size, 0), dtype=np.uint8)
+        assert np.array_equal(got, want)
+    finally:
+        os.close(fd)
+    d_tile = torch.zeros((4, 8), dtype=torch.int32, device="cuda")
+    with pytest.raises(_capi.RtiError):
+        _capi.call("rti_table_tile_to_file", d_tile.data_ptr(), 8, 4, 8, 1 << 20, offsets.ctypes.data, 0, None, None)
+    _capi.call("rti_destroy")
+
+
 def _fit_soa(torch, lx, ly, inten):
     from rti_b200 import _capi
     p, n = lx.shape
