@@ -841,7 +841,7 @@ def _table_to_host_tiled(res):
     from concurrent.futures import ThreadPoolExecutor
     gg = res.axis.size ** 2
     out = np.empty((gg, res.rows, res.cols), dtype=np.int32)
-    if os.environ.get("RTI_TABLE_TO_HOST", "native") != "python":
+    if gg > 0 and os.environ.get("RTI_TABLE_TO_HOST", "native") != "python":
         torch = _torch()
         p = res.rows * res.cols
         for r0, tr, d_tile, ev in table_tiles(res, with_events=True):
@@ -999,7 +999,9 @@ def write_table_file(res, filename):
     writer = table_io.TableTileWriter(g, g, (res.rows, res.cols), np.int32, filename)
     threads = max(1, min(8, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else 4))
     try:
-        if os.environ.get("RTI_TABLE_TO_HOST", "native") != "python":
+        if g == 0:
+            pass                                     # an empty light grid: the file is the empty list already
+        elif os.environ.get("RTI_TABLE_TO_HOST", "native") != "python":
             # row tiles of the ROI: device tile -> (int16 over PCIe when it fits) -> pinned ring -> host threads
             # that pwrite each image's rows at its fixed offset (rti_table_tile_to_file); the evaluation of the
             # next tile runs meanwhile
